@@ -1,0 +1,166 @@
+/*
+ * soar_b200.h — C ABI of the B200-native SOAR render-loop kernels.
+ *
+ * This is the drop-in boundary. Every entry point names the
+ * reference interface it replaces; paths are relative to the reference tree
+ * (DGR = submodules/diff-gaussian-rasterization, KNN = submodules/simple-knn,
+ * TS = soar/threestudio-soar).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types. All pointers are DEVICE
+ *     pointers to contiguous float32/int32 unless the name ends in `_host`.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - the library keeps no global state besides a thread-local error string;
+ *     every scratch buffer is caller-owned (the python shim allocates them with
+ *     torch and keeps them in the autograd ctx, like the reference does through
+ *     its resize_ callbacks, DGR/rasterize_points.cu:27-33).
+ *   - return 0 on success, negative SOAR_E_* on error; soar_last_error() gives
+ *     the message (the shim re-raises it as RuntimeError like the reference's
+ *     C++ exceptions, DGR/rasterize_points.cu:50-52).
+ */
+#ifndef SOAR_B200_H_INCLUDED
+#define SOAR_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SOAR_OK 0
+#define SOAR_E_INVALID (-1)  /* bad argument (shape, null pointer, size)        */
+#define SOAR_E_CUDA (-2)     /* a CUDA runtime call or launch failed            */
+#define SOAR_E_WORKSPACE (-3) /* caller-provided scratch buffer too small       */
+#define SOAR_E_PREFILTER (-4) /* prefiltered=1 but a Gaussian was culled
+                                 (reference: device __trap, DGR auxiliary.h:163) */
+
+typedef void* soar_stream_t;
+
+/* One view = GaussianRasterizationSettings + the per-call tensors
+ * (DGR/diff_gaussian_rasterization/__init__.py:267-284 and the 24-argument
+ * tuple at :77-102 <-> DGR/rasterize_points.h:18-32). Matrices are in the
+ * reference's row-vector convention, i.e. read column-major by the kernels
+ * (DGR/cuda_rasterizer/auxiliary.h:65-84). */
+typedef struct SoarRastView {
+  int32_t P;          /* number of Gaussians                                    */
+  int32_t sh_degree;  /* active SH degree D (0..3)                              */
+  int32_t M;          /* SH coefficients per Gaussian (0 when colors_precomp)   */
+  int32_t width, height;
+  float tanfovx, tanfovy, scale_modifier;
+  int32_t prefiltered, render_front, sort_descending, debug;
+  const float* bg;             /* [3]                                            */
+  const float* means3D;        /* [P,3]                                          */
+  const float* shs;            /* [P,M,3] or NULL                                */
+  const float* colors_precomp; /* [P,3]   or NULL                                */
+  const float* opacities;      /* [P]                                            */
+  const float* scales;         /* [P,3]   or NULL                                */
+  const float* rotations;      /* [P,4] (w,x,y,z), NOT normalised by the kernel  */
+  const float* cov3D_precomp;  /* [P,6]   or NULL                                */
+  const float* viewmatrix;     /* [16]                                           */
+  const float* projmatrix;     /* [16]                                           */
+  const float* prcppoint;      /* [2]                                            */
+  const float* patch_bbox;     /* [4] = (h0,w0,h1,w1)                            */
+  const float* campos;         /* [3]                                            */
+  const float* config;         /* [4] = (surface,normalize_depth,perpix_depth,lrn_cam) */
+} SoarRastView;
+
+/* Gradient outputs of the rasterizer backward: the 11-tuple returned by
+ * RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187). The kernels
+ * write EVERY element (zeros for culled Gaussians), so the caller may pass
+ * uninitialised memory — the reference needs 15 torch::zeros fills (:133-147). */
+typedef struct SoarRastGrads {
+  float* dL_dmeans2D;   /* [P,3]  NDC-scaled screen gradient, .z = 0            */
+  float* dL_dcolors;    /* [P,3]                                                */
+  float* dL_dopacity;   /* [P,1]                                                */
+  float* dL_dmeans3D;   /* [P,3]                                                */
+  float* dL_dcov3D;     /* [P,6]                                                */
+  float* dL_dsh;        /* [P,M,3] (may be NULL when M == 0)                    */
+  float* dL_dscales;    /* [P,3]                                                */
+  float* dL_drotations; /* [P,4]                                                */
+  float* dL_dviewmat;   /* [16]  nonzero only when config[3] > 0                */
+  float* dL_dprojmat;   /* [16]                                                 */
+  float* dL_dcampos;    /* [3]                                                  */
+} SoarRastGrads;
+
+/* ---- rasterizer (replaces DGR `_C.rasterize_gaussians`, DGR/ext.cpp:16 ->
+ *      RasterizeGaussiansCUDA -> CudaRasterizer::Rasterizer::forward,
+ *      DGR/cuda_rasterizer/rasterizer_impl.cu:188-312) -------------------------- */
+
+/* Sizes of the caller-owned scratch buffers (reference: required<State>(),
+ * DGR/cuda_rasterizer/rasterizer_impl.h:74-84). */
+size_t soar_rast_geom_bytes(int32_t P);
+size_t soar_rast_image_bytes(int32_t width, int32_t height);
+size_t soar_rast_binning_bytes(uint32_t num_rendered, int32_t width, int32_t height);
+
+/* Phase 1 (K1+K2): per-Gaussian preprocess + decoupled-look-back prefix sum of
+ * tiles_touched. Writes radii[P], fills `geom`, and returns num_rendered
+ * through *num_rendered_host after synchronising `stream` (the reference blocks
+ * at the same point, rasterizer_impl.cu:250). */
+int soar_rast_forward_bin(const SoarRastView* view, void* geom, size_t geom_bytes,
+                          int32_t* radii, uint32_t* num_rendered_host, soar_stream_t stream);
+
+/* Phase 2 (K3..K6): key duplication, onesweep radix sort of tile|depth keys,
+ * tile ranges, tile alpha-blend. Outputs: color[3,H,W] normal[3,H,W]
+ * depth[1,H,W] opac[1,H,W]; every pixel is written. */
+int soar_rast_forward_render(const SoarRastView* view, void* geom, void* binning,
+                             size_t binning_bytes, void* img, size_t img_bytes,
+                             uint32_t num_rendered, float* out_color, float* out_normal,
+                             float* out_depth, float* out_opac, soar_stream_t stream);
+
+/* Backward (replaces `_C.rasterize_gaussians_backward`, DGR/ext.cpp:17 ->
+ * Rasterizer::backward, rasterizer_impl.cu:316-379). `geom`, `binning`, `img`
+ * are the buffers filled by the forward of the same view. `scratch` must hold
+ * soar_rast_backward_scratch_bytes(P) bytes. */
+size_t soar_rast_backward_scratch_bytes(int32_t P);
+int soar_rast_backward(const SoarRastView* view, const int32_t* radii, const void* geom,
+                       const void* binning, const void* img, uint32_t num_rendered,
+                       const float* dL_dout_color, const float* dL_dout_normal,
+                       const float* dL_dout_depth, const float* dL_dout_opac,
+                       void* scratch, size_t scratch_bytes, const SoarRastGrads* grads,
+                       soar_stream_t stream);
+
+/* Replaces `_C.mark_visible` (DGR/ext.cpp:18). The reference kernel body is
+ * commented out (rasterizer_impl.cu:52-62): `present` is left untouched, so the
+ * all-false tensor the caller allocated is what comes back. */
+int soar_rast_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                           const float* projmatrix, uint8_t* present, soar_stream_t stream);
+
+/* Debug accessors for parity tests: device pointers into the
+ * private scratch layout. what: 0 sorted keys u64[R], 1 point_list u32[R],
+ * 2 ranges uint2[tiles], 3 n_contrib u32[W*H], 4 final_T f32[W*H],
+ * 5 tiles_touched u32[P], 6 point_offsets u32[P], 7 records f32[P*24]. */
+const void* soar_rast_debug_ptr(int what, int32_t P, int32_t width, int32_t height,
+                                uint32_t num_rendered, const void* geom, const void* binning,
+                                const void* img);
+
+/* ---- KNN (replaces `simple_knn._C.distCUDA2`, KNN/ext.cpp:15-17 ->
+ *      SimpleKNN::knn, KNN/simple_knn.cu:186-222) ------------------------------- */
+size_t soar_knn_workspace_bytes(int32_t P);
+int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* workspace,
+                   size_t workspace_bytes, soar_stream_t stream);
+
+/* ---- LBS skinning (replaces the torch op chain at
+ *      TS/utils/smpl.py:613 (weights x bones blend) and
+ *      TS/renderer/diff_gaussian_rasterizer.py:103-114 (apply to points/quats)) -- */
+/* weights[N,J] (row-major), bones[J,16] row-major 4x4 (cano->live), points[N,3],
+ * quats[N,4] (w,x,y,z). axis_perm: 0 = none (gt views, :138-149),
+ * 1 = the SDS-view swizzle (x,y,z)->(z,x,y) of transform_point_cloud("+z,+x,+y"). */
+int soar_lbs_forward(const float* weights, const float* bones, int32_t J, const float* points,
+                     const float* quats, int32_t N, int32_t axis_perm, float* out_points,
+                     float* out_quats, float* out_mats /* [N,12] or NULL */,
+                     soar_stream_t stream);
+/* `mats` is the [N,12] per-point transform the forward wrote to out_mats (the
+ * backward reads 48 B/point instead of re-blending the 220-byte weight row). */
+int soar_lbs_backward(const float* mats, const float* quats, int32_t N, int32_t axis_perm,
+                      const float* dL_dout_points, const float* dL_dout_quats,
+                      float* dL_dpoints, float* dL_dquats, soar_stream_t stream);
+
+/* ---- misc -------------------------------------------------------------------- */
+const char* soar_last_error(void);
+int soar_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SOAR_B200_H_INCLUDED */

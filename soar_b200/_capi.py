@@ -1,0 +1,143 @@
+"""ctypes binding of libsoar_b200.so — the C-ABI declared in include/soar_b200.h.
+
+This is the only place that touches the shared library. There is no CPU
+fallback: if the library is missing or was not built, importing the product
+modules raises, and every entry point turns a non-zero return code into a
+RuntimeError carrying soar_last_error() (the reference surfaces C++ exceptions
+as RuntimeError the same way, DGR/rasterize_points.cu:50-52).
+"""
+import ctypes
+import os
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int32, c_size_t, c_uint8, c_uint32, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsoar_b200.so")
+
+c_float_p = c_void_p  # device pointers travel as integers
+
+
+class SoarRastView(Structure):
+    _fields_ = [
+        ("P", c_int32),
+        ("sh_degree", c_int32),
+        ("M", c_int32),
+        ("width", c_int32),
+        ("height", c_int32),
+        ("tanfovx", c_float),
+        ("tanfovy", c_float),
+        ("scale_modifier", c_float),
+        ("prefiltered", c_int32),
+        ("render_front", c_int32),
+        ("sort_descending", c_int32),
+        ("debug", c_int32),
+        ("bg", c_void_p),
+        ("means3D", c_void_p),
+        ("shs", c_void_p),
+        ("colors_precomp", c_void_p),
+        ("opacities", c_void_p),
+        ("scales", c_void_p),
+        ("rotations", c_void_p),
+        ("cov3D_precomp", c_void_p),
+        ("viewmatrix", c_void_p),
+        ("projmatrix", c_void_p),
+        ("prcppoint", c_void_p),
+        ("patch_bbox", c_void_p),
+        ("campos", c_void_p),
+        ("config", c_void_p),
+    ]
+
+
+class SoarRastGrads(Structure):
+    _fields_ = [
+        ("dL_dmeans2D", c_void_p),
+        ("dL_dcolors", c_void_p),
+        ("dL_dopacity", c_void_p),
+        ("dL_dmeans3D", c_void_p),
+        ("dL_dcov3D", c_void_p),
+        ("dL_dsh", c_void_p),
+        ("dL_dscales", c_void_p),
+        ("dL_drotations", c_void_p),
+        ("dL_dviewmat", c_void_p),
+        ("dL_dprojmat", c_void_p),
+        ("dL_dcampos", c_void_p),
+    ]
+
+
+# name -> (restype, argtypes); mirrors include/soar_b200.h one to one
+SIGNATURES = {
+    "soar_rast_geom_bytes": (c_size_t, [c_int32]),
+    "soar_rast_image_bytes": (c_size_t, [c_int32, c_int32]),
+    "soar_rast_binning_bytes": (c_size_t, [c_uint32, c_int32, c_int32]),
+    "soar_rast_forward_bin": (
+        c_int32,
+        [POINTER(SoarRastView), c_void_p, c_size_t, c_void_p, POINTER(c_uint32), c_void_p],
+    ),
+    "soar_rast_forward_render": (
+        c_int32,
+        [POINTER(SoarRastView), c_void_p, c_void_p, c_size_t, c_void_p, c_size_t, c_uint32,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_rast_backward_scratch_bytes": (c_size_t, [c_int32]),
+    "soar_rast_backward": (
+        c_int32,
+        [POINTER(SoarRastView), c_void_p, c_void_p, c_void_p, c_void_p, c_uint32, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, POINTER(SoarRastGrads), c_void_p],
+    ),
+    "soar_rast_mark_visible": (c_int32, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "soar_rast_debug_ptr": (
+        c_void_p,
+        [c_int32, c_int32, c_int32, c_int32, c_uint32, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_knn_workspace_bytes": (c_size_t, [c_int32]),
+    "soar_knn_dist2": (c_int32, [c_void_p, c_int32, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "soar_lbs_forward": (
+        c_int32,
+        [c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
+         c_void_p, c_void_p],
+    ),
+    "soar_lbs_backward": (
+        c_int32,
+        [c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_last_error": (c_char_p, []),
+    "soar_version": (c_int32, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libsoar_b200.so (once). Raises ImportError with build instructions if absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `bash soar_b200/csrc/build.sh` "
+            "(or `python -c 'import __graft_entry__ as g; g.build()'`). "
+            "There is no CPU fallback for the render path."
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error():
+    msg = load().soar_last_error()
+    return msg.decode("utf-8", "replace") if msg else ""
+
+
+def check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"{what} failed (code {rc}): {last_error()}")
+
+
+def ptr(t):
+    """Device pointer of a tensor, or None for an absent / empty one."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()

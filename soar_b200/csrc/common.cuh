@@ -1,0 +1,134 @@
+// Shared helpers for the sm_100a kernels: error plumbing, tile constants,
+// column-major 3x3 algebra with a fixed summation order, relaxed loads/stores
+// for the decoupled look-back protocols.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/soar_b200.h"
+
+namespace soar {
+
+// Tile geometry is part of the bit-exact contract (DGR/cuda_rasterizer/config.h:14-16).
+constexpr int TILE_X = 16;
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+void set_error(const char* fmt, ...);
+
+#define SOAR_CUDA_TRY(expr)                                                          \
+  do {                                                                               \
+    cudaError_t _e = (expr);                                                         \
+    if (_e != cudaSuccess) {                                                         \
+      ::soar::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),      \
+                        __FILE__, __LINE__);                                         \
+      return SOAR_E_CUDA;                                                            \
+    }                                                                                \
+  } while (0)
+
+#define SOAR_LAUNCH_CHECK(name)                                                      \
+  do {                                                                               \
+    cudaError_t _e = cudaGetLastError();                                             \
+    if (_e != cudaSuccess) {                                                         \
+      ::soar::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));    \
+      return SOAR_E_CUDA;                                                            \
+    }                                                                                \
+  } while (0)
+
+__host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+__host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// Number of sort bits above the 32 depth bits: the reference's getHigherMsb()
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:35-48) restated as "smallest b with
+// n >> b == 0" — identical for every n >= 1.
+inline int tile_id_bits(uint32_t n_tiles) {
+  int b = 0;
+  while (b < 32 && (n_tiles >> b) != 0) ++b;
+  return b;
+}
+
+// ---- column-major 3x3 (m[c][r]) with the summation order k = 0,1,2 -----------
+// The per-Gaussian algebra must round like the reference's (which goes through
+// a column-major header library); products are therefore always accumulated
+// over the inner index in ascending order, left-associated.
+struct Mat3 {
+  float m[3][3];  // m[col][row]
+};
+
+__device__ __forceinline__ Mat3 mat3_cols(float a, float b, float c, float d, float e, float f,
+                                          float g, float h, float i) {
+  Mat3 r;
+  r.m[0][0] = a; r.m[0][1] = b; r.m[0][2] = c;
+  r.m[1][0] = d; r.m[1][1] = e; r.m[1][2] = f;
+  r.m[2][0] = g; r.m[2][1] = h; r.m[2][2] = i;
+  return r;
+}
+
+__device__ __forceinline__ Mat3 mat3_mul(const Mat3& A, const Mat3& B) {
+  Mat3 r;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int w = 0; w < 3; ++w)
+      r.m[c][w] = A.m[0][w] * B.m[c][0] + A.m[1][w] * B.m[c][1] + A.m[2][w] * B.m[c][2];
+  return r;
+}
+
+__device__ __forceinline__ Mat3 mat3_transpose(const Mat3& A) {
+  Mat3 r;
+#pragma unroll
+  for (int c = 0; c < 3; ++c)
+#pragma unroll
+    for (int w = 0; w < 3; ++w) r.m[c][w] = A.m[w][c];
+  return r;
+}
+
+// ---- matrices in the row-vector convention, read column-major -----------------
+__device__ __forceinline__ float3 xform_point_4x3(const float3& p, const float* m) {
+  return make_float3(m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12],
+                     m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+                     m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14]);
+}
+__device__ __forceinline__ float4 xform_point_4x4(const float3& p, const float* m) {
+  return make_float4(m[0] * p.x + m[4] * p.y + m[8] * p.z + m[12],
+                     m[1] * p.x + m[5] * p.y + m[9] * p.z + m[13],
+                     m[2] * p.x + m[6] * p.y + m[10] * p.z + m[14],
+                     m[3] * p.x + m[7] * p.y + m[11] * p.z + m[15]);
+}
+__device__ __forceinline__ float3 xform_vec_4x3(const float3& p, const float* m) {
+  return make_float3(m[0] * p.x + m[4] * p.y + m[8] * p.z,
+                     m[1] * p.x + m[5] * p.y + m[9] * p.z,
+                     m[2] * p.x + m[6] * p.y + m[10] * p.z);
+}
+__device__ __forceinline__ float3 xform_vec_4x3_T(const float3& p, const float* m) {
+  return make_float3(m[0] * p.x + m[1] * p.y + m[2] * p.z,
+                     m[4] * p.x + m[5] * p.y + m[6] * p.z,
+                     m[8] * p.x + m[9] * p.y + m[10] * p.z);
+}
+
+// ---- relaxed gpu-scope accesses for single-word status protocols ---------------
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+}  // namespace soar

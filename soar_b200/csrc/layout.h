@@ -1,0 +1,123 @@
+// Private layout of the three caller-owned scratch buffers (geom / binning / img).
+// Plays the role of GeometryState / BinningState / ImageState
+// (DGR/cuda_rasterizer/rasterizer_impl.h:22-84) but the layout is our own:
+//   * one 96-byte, 32-byte-sector-aligned record per Gaussian holding exactly the
+//     floats the blend kernels gather (the reference scatters them over 8 arrays
+//     and carries 10 Jinv floats of which only 6 are ever read);
+//   * keys/values double buffers for the onesweep passes + its histograms and
+//     look-back status words;
+//   * per-pixel final_T / n_contrib / final_D and per-tile ranges.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+#include "common.cuh"
+
+namespace soar {
+
+// ---- per-Gaussian record (24 floats = 96 B = 3 sectors) ------------------------
+constexpr int REC_FLOATS = 24;
+enum RecSlot {
+  REC_X = 0, REC_Y = 1, REC_CON_A = 2, REC_CON_B = 3,      // float4 #0
+  REC_CON_C = 4, REC_OPAC = 5, REC_DEPTH = 6, REC_J6 = 7,  // float4 #1
+  REC_R = 8, REC_G = 9, REC_B = 10, REC_J9 = 11,           // float4 #2
+  REC_NX = 12, REC_NY = 13, REC_NZ = 14, REC_VIEWCOS = 15, // float4 #3
+  REC_J0 = 16, REC_J1 = 17, REC_J2 = 18, REC_J3 = 19,      // float4 #4
+  REC_RECT_X = 20, REC_RECT_Y = 21, REC_RADIUS = 22, REC_PAD = 23  // float4 #5 (bit-cast ints)
+};
+
+// ---- decoupled look-back scan of tiles_touched ----------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+struct GeomLayout {
+  size_t records;        // float[P*24]
+  size_t tiles_touched;  // u32[P]
+  size_t point_offsets;  // u32[P] inclusive prefix sum
+  size_t scan_status;    // u64[n_scan_tiles] + u32 ticket + u32 error flag (zeroed per call)
+  size_t scan_status_bytes;
+  size_t total;
+};
+
+inline GeomLayout geom_layout(size_t P) {
+  GeomLayout L;
+  size_t off = 0;
+  L.records = off;        off = align_up(off + P * REC_FLOATS * sizeof(float), 256);
+  L.tiles_touched = off;  off = align_up(off + P * sizeof(uint32_t), 256);
+  L.point_offsets = off;  off = align_up(off + P * sizeof(uint32_t), 256);
+  size_t n_tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
+  L.scan_status = off;
+  L.scan_status_bytes = align_up(n_tiles * sizeof(uint64_t) + 16, 256);
+  off += L.scan_status_bytes;
+  L.total = off + 256;
+  return L;
+}
+
+// ---- per-pixel / per-tile state ---------------------------------------------------
+struct ImageLayout {
+  size_t final_T;    // f32[W*H]
+  size_t n_contrib;  // u32[W*H]
+  size_t final_D;    // f32[W*H]
+  size_t ranges;     // uint2[tiles]
+  size_t total;
+};
+
+inline ImageLayout image_layout(int W, int H) {
+  ImageLayout L;
+  size_t N = (size_t)W * H;
+  size_t tiles = (size_t)ceil_div(W, TILE_X) * ceil_div(H, TILE_Y);
+  size_t off = 0;
+  L.final_T = off;   off = align_up(off + N * 4, 256);
+  L.n_contrib = off; off = align_up(off + N * 4, 256);
+  L.final_D = off;   off = align_up(off + N * 4, 256);
+  L.ranges = off;    off = align_up(off + tiles * 8, 256);
+  L.total = off + 256;
+  return L;
+}
+
+// ---- onesweep radix sort ------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 8;
+
+struct BinningLayout {
+  size_t keys[2];    // u64[R] x2 (ping-pong)
+  size_t values[2];  // u32[R] x2
+  size_t ghist;      // u32[SORT_MAX_PASSES*256] digit histograms -> exclusive offsets
+  size_t status;     // u32[passes*n_sort_tiles*256] look-back words + u32 ticket per pass
+  size_t zero_begin, zero_bytes;  // region that must be zero before sorting (ghist+status)
+  size_t total;
+  int n_sort_tiles;
+};
+
+inline BinningLayout binning_layout(size_t R, int passes) {
+  BinningLayout L;
+  size_t off = 0;
+  L.keys[0] = off;   off = align_up(off + R * 8, 256);
+  L.keys[1] = off;   off = align_up(off + R * 8, 256);
+  L.values[0] = off; off = align_up(off + R * 4, 256);
+  L.values[1] = off; off = align_up(off + R * 4, 256);
+  L.n_sort_tiles = (int)((R + SORT_TILE - 1) / SORT_TILE);
+  L.zero_begin = off;
+  L.ghist = off;     off = align_up(off + SORT_MAX_PASSES * SORT_RADIX * 4, 256);
+  L.status = off;
+  off = align_up(off + ((size_t)passes * L.n_sort_tiles * SORT_RADIX + SORT_MAX_PASSES) * 4, 256);
+  L.zero_bytes = off - L.zero_begin;
+  L.total = off + 256;
+  return L;
+}
+
+inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
+
+// ---- backward scratch: per-Gaussian accumulator written by the blend backward ----
+// 16 floats: dcolor[3] dnormal[3] ddepth dmean2D.xy dconic.(a,b,c) dopacity pad[3]
+constexpr int GACC_FLOATS = 16;
+enum GaccSlot {
+  GA_DC0 = 0, GA_DC1 = 1, GA_DC2 = 2, GA_DN0 = 3, GA_DN1 = 4, GA_DN2 = 5, GA_DD = 6,
+  GA_DMX = 7, GA_DMY = 8, GA_DCA = 9, GA_DCB = 10, GA_DCC = 11, GA_DO = 12
+};
+
+}  // namespace soar

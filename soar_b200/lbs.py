@@ -1,0 +1,82 @@
+"""Skinning of canonical Gaussians with SMPL-X bone transforms on the sm_100a
+kernel (soar_b200/csrc/lbs.cu) — one fused op for the reference's torch chain:
+
+    pt_mats = einsum("bnj,bjxy->bnxy", weights, cano2live_jnt_mats)   TS/utils/smpl.py:613
+    points  = einsum("bnxy,bny->bnx", mat[..., :3, :3], points) + mat[..., :3, 3]
+    points, T = transform_point_cloud(points, "+z,+x,+y")              (SDS views only)
+    rot_mat = T.T @ (mat[..., :3, :3] @ quaternion_to_matrix(rot))
+    rot     = normalize(matrix_to_quaternion(rot_mat))
+                                   TS/renderer/diff_gaussian_rasterizer.py:103-114 / :138-149
+
+Gradients flow to `points` and `rot` only: the reference detaches the skin
+weights (TS/utils/smpl.py:611) and the pose tensors are plain buffers (:543-545).
+"""
+import ctypes
+
+import torch
+
+from . import _capi
+
+_lib = _capi.load()
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class _SkinGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, points, quats, weights, bones, swizzle):
+        N, J = weights.shape
+        points_c = points.detach().float().contiguous()
+        quats_c = quats.detach().float().contiguous()
+        weights_c = weights.detach().float().contiguous()
+        bones_c = bones.detach().float().reshape(J, 16).contiguous()
+        dev = points.device
+        out_p = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        out_q = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        mats = torch.empty((N, 12), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _capi.check(_lib.soar_lbs_forward(_capi.ptr(weights_c), bones_c.data_ptr(), J,
+                                              _capi.ptr(points_c), _capi.ptr(quats_c), N,
+                                              int(swizzle), _capi.ptr(out_p), _capi.ptr(out_q),
+                                              _capi.ptr(mats), _stream()), "soar_lbs_forward")
+        ctx.save_for_backward(mats, quats_c)
+        ctx.swizzle = int(swizzle)
+        ctx.mark_non_differentiable(mats)
+        return out_p, out_q, mats
+
+    @staticmethod
+    def backward(ctx, g_points, g_quats, _g_mats):
+        mats, quats = ctx.saved_tensors
+        N = quats.shape[0]
+        dev = quats.device
+        if g_points is None:
+            g_points = torch.zeros((N, 3), dtype=torch.float32, device=dev)
+        if g_quats is None:
+            g_quats = torch.zeros((N, 4), dtype=torch.float32, device=dev)
+        g_points = g_points.float().contiguous()
+        g_quats = g_quats.float().contiguous()
+        d_points = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        d_quats = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _capi.check(_lib.soar_lbs_backward(_capi.ptr(mats), _capi.ptr(quats), N, ctx.swizzle,
+                                               _capi.ptr(g_points), _capi.ptr(g_quats),
+                                               _capi.ptr(d_points), _capi.ptr(d_quats), _stream()),
+                        "soar_lbs_backward")
+        return d_points, d_quats, None, None, None
+
+
+def skin_gaussians(points, quats, weights, bones, swizzle=False):
+    """points [N,3], quats [N,4] (w,x,y,z), weights [N,J] (detached), bones [J,4,4] or [1,J,4,4]
+    (cano->live) -> (points' [N,3], quats' [N,4] unit, pt_mats [N,12] = rows 0..2 of the blended 4x4).
+    swizzle=True applies the SDS-view axis change (x,y,z)->(z,x,y)."""
+    if not points.is_cuda:
+        raise RuntimeError("skin_gaussians: CUDA tensors required (there is no CPU path)")
+    bones = bones.reshape(-1, 4, 4)
+    if weights.dim() == 3:
+        weights = weights[0]
+    if weights.shape[0] != points.shape[0] or weights.shape[1] != bones.shape[0]:
+        raise RuntimeError(f"skin_gaussians: weights {tuple(weights.shape)} do not match "
+                           f"{points.shape[0]} points x {bones.shape[0]} bones")
+    return _SkinGaussians.apply(points, quats, weights, bones, swizzle)

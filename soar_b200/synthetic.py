@@ -1,0 +1,179 @@
+"""Deterministic synthetic inputs for tests and bench: SMPL-X assets and
+videos are not available offline, so Gaussians, cameras, cotangents and an SMPL-X-shaped
+skinning problem are generated from fixed seeds with numpy's PCG64 (bit-identical on
+every machine), returned as CPU float32 torch tensors.
+
+Cameras are built exactly like the reference does it
+(TS/renderer/gaussian_batch_renderer.py:401-471: convert_pose, get_projection_matrix_gaussian,
+get_cam_info_gaussian_cxcy), i.e. row-vector matrices that the kernels read column-major.
+"""
+import math
+
+import numpy as np
+import torch
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32))
+
+
+def look_at_c2w(eye, target=(0.0, 0.0, 0.0), up=(0.0, 1.0, 0.0)):
+    """OpenGL-style camera-to-world (camera looks down -z, +y up), as threestudio produces."""
+    eye, target, up = (np.asarray(v, dtype=np.float64) for v in (eye, target, up))
+    f = target - eye
+    f /= np.linalg.norm(f)
+    r = np.cross(f, up)
+    r /= np.linalg.norm(r)
+    u = np.cross(r, f)
+    c2w = np.eye(4)
+    c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3] = r, u, -f, eye
+    return c2w
+
+
+def camera(c2w, fovx, fovy, znear=0.1, zfar=100.0):
+    """-> (world_view_transform [4,4], full_proj_transform [4,4], camera_center [3]) float32."""
+    flip = np.diag([1.0, -1.0, -1.0, 1.0])
+    w2c = np.linalg.inv(c2w @ flip)
+    world_view = w2c.T.astype(np.float32)
+    top = math.tan(fovy / 2) * znear
+    right = math.tan(fovx / 2) * znear
+    Pm = np.zeros((4, 4), dtype=np.float32)
+    Pm[0, 0] = 2.0 * znear / (2 * right)
+    Pm[1, 1] = 2.0 * znear / (2 * top)
+    Pm[3, 2] = 1.0
+    Pm[2, 2] = (zfar + znear) / (zfar - znear)
+    Pm[2, 3] = -(zfar * znear) / (zfar - znear)
+    full = (world_view @ Pm.T).astype(np.float32)
+    center = np.linalg.inv(world_view.astype(np.float64))[3, :3].astype(np.float32)
+    return _t(world_view), _t(full), _t(center)
+
+
+def ring_cameras(n_views, W, H, seed=0, fovy_deg=40.0, dist=(2.5, 3.0), elev_deg=(-10.0, 20.0)):
+    """n_views cameras on a ring of azimuths looking at the origin (SDS-style, §8d)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 7919))
+    fovy = math.radians(fovy_deg)
+    fovx = 2 * math.atan(math.tan(fovy / 2) * W / H)
+    cams = []
+    for v in range(n_views):
+        az = 2 * math.pi * v / max(n_views, 1) + rng.uniform(-0.05, 0.05)
+        el = math.radians(rng.uniform(*elev_deg))
+        d = rng.uniform(*dist)
+        eye = (d * math.cos(el) * math.sin(az), d * math.sin(el), d * math.cos(el) * math.cos(az))
+        view, proj, center = camera(look_at_c2w(eye), fovx, fovy)
+        cams.append(dict(viewmatrix=view, projmatrix=proj, campos=center,
+                         tanfovx=math.tan(fovx / 2), tanfovy=math.tan(fovy / 2)))
+    return cams
+
+
+def gaussians(P, sh_degree=None, seed=0, surfel=False):
+    """"random" distribution of §8d. sh_degree=None -> precomputed colours.
+    surfel=True reproduces SOAR's usage: opacity 1, scale.z = -1e10 (Q7), isotropic in-plane."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    means = rng.uniform(-1.0, 1.0, size=(P, 3)) * 0.9
+    log_s = rng.uniform(math.log(0.003), math.log(0.03), size=(P, 3))
+    scales = np.exp(log_s)
+    q = rng.normal(size=(P, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    opac = 1.0 / (1.0 + np.exp(-rng.normal(scale=1.5, size=(P, 1))))
+    out = dict(means3D=_t(means), rotations=_t(q))
+    if surfel:
+        scales[:, 1] = scales[:, 0]
+        scales[:, 2] = -1e10
+        opac = np.ones((P, 1))
+    out["scales"] = _t(scales)
+    out["opacities"] = _t(opac)
+    if sh_degree is None:
+        out["colors_precomp"] = _t(rng.uniform(0.0, 1.0, size=(P, 3)))
+        out["shs"] = None
+    else:
+        M = (sh_degree + 1) ** 2
+        sh = rng.normal(scale=0.3, size=(P, M, 3))
+        sh[:, 0, :] = rng.normal(scale=1.0, size=(P, 3))
+        out["shs"] = _t(sh)
+        out["colors_precomp"] = None
+    return out
+
+
+def cotangents(W, H, seed=0):
+    """Fixed-seed N(0,1) cotangents for all four image outputs (§8d loss)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 104729))
+    return dict(color=_t(rng.normal(size=(3, H, W))), normal=_t(rng.normal(size=(3, H, W))),
+                depth=_t(rng.normal(size=(1, H, W))), opac=_t(rng.normal(size=(1, H, W))))
+
+
+def scene(P, W, H, sh_degree=None, seed=0, surfel=False, config=None, bg=(0.0, 0.0, 0.0),
+          sort_descending=False, render_front=False, view=0, n_views=1):
+    """One view of a synthetic scene: everything GaussianRasterizationSettings and the
+    rasterizer call need, as CPU tensors / python scalars."""
+    g = gaussians(P, sh_degree=sh_degree, seed=seed, surfel=surfel)
+    cam = ring_cameras(max(n_views, 1), W, H, seed=seed)[view]
+    if config is None:
+        config = (1.0, 1.0, 1.0, 0.0) if surfel else (0.0, 0.0, 0.0, 0.0)
+    g.update(cam)
+    g.update(dict(image_height=H, image_width=W, bg=_t(bg), scale_modifier=1.0,
+                  patch_bbox=_t([0.0, 0.0, float(H), float(W)]), prcppoint=_t([0.5, 0.5]),
+                  sh_degree=0 if sh_degree is None else sh_degree, prefiltered=False,
+                  render_front=render_front, sort_descending=sort_descending, debug=False,
+                  config=_t(config)))
+    return g
+
+
+# ---------------------------------------------------------------------------------------------
+# SMPL-X-shaped skinning problem (55 joints, 10,475 canonical vertices)
+# ---------------------------------------------------------------------------------------------
+SMPLX_PARENTS = [-1, 0, 0, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 9, 9, 12, 13, 14, 16, 17, 18, 19, 15, 15,
+                 15, 20, 25, 26, 20, 28, 29, 20, 31, 32, 20, 34, 35, 20, 37, 38, 21, 40, 41, 21, 43,
+                 44, 21, 46, 47, 21, 49, 50, 21, 52, 53]
+N_JOINTS = 55
+N_VERTS = 10475
+
+
+def _rodrigues(rv):
+    ang = np.linalg.norm(rv + 1e-8, axis=-1, keepdims=True)  # Q16: eps added per component
+    ax = rv / ang
+    c, s = np.cos(ang)[..., None], np.sin(ang)[..., None]
+    K = np.zeros(rv.shape[:-1] + (3, 3))
+    K[..., 0, 1], K[..., 0, 2] = -ax[..., 2], ax[..., 1]
+    K[..., 1, 0], K[..., 1, 2] = ax[..., 2], -ax[..., 0]
+    K[..., 2, 0], K[..., 2, 1] = -ax[..., 1], ax[..., 0]
+    return np.eye(3) + s * K + (1 - c) * (K @ K)
+
+
+def skinning_problem(N, seed=0):
+    """Synthetic humanoid: joints along a capsule skeleton, `N` canonical Gaussians near the
+    bones, skin weights = top-4 softmax(-d^2/sigma^2) over joints (sigma 0.08 m), bone
+    transforms cano->live from a random pose pushed through the SMPL-X kinematic tree
+    (TS/utils/smplx/lbs.py:343-396) with transl (0, 0.3, 0) folded in (Q17)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 31337))
+    J = N_JOINTS
+    joints = np.zeros((J, 3))
+    for j in range(1, J):
+        p = SMPLX_PARENTS[j]
+        step = rng.normal(size=3)
+        step[1] = -abs(step[1]) if j in (1, 2, 4, 5, 7, 8, 10, 11) else abs(step[1])
+        step /= np.linalg.norm(step)
+        joints[j] = joints[p] + step * (0.12 if j < 22 else 0.03)
+    seg = rng.integers(1, J, size=N)
+    t = rng.uniform(size=(N, 1))
+    pts = joints[np.asarray(SMPLX_PARENTS)[seg]] * (1 - t) + joints[seg] * t
+    pts += rng.normal(scale=0.03, size=(N, 3))
+    d2 = ((pts[:, None, :] - joints[None]) ** 2).sum(-1)
+    logits = -d2 / (0.08 ** 2)
+    kth = np.partition(logits, -4, axis=1)[:, -4][:, None]
+    w = np.where(logits >= kth, np.exp(logits - logits.max(1, keepdims=True)), 0.0)
+    w /= w.sum(1, keepdims=True)
+    pose = rng.normal(scale=0.3, size=(J, 3))
+    pose[0] = 0.0
+    Rm = _rodrigues(pose)
+    G = np.zeros((J, 4, 4))
+    for j in range(J):
+        local = np.eye(4)
+        local[:3, :3] = Rm[j]
+        local[:3, 3] = joints[j] - (joints[SMPLX_PARENTS[j]] if j else 0.0)
+        G[j] = local if j == 0 else G[SMPLX_PARENTS[j]] @ local
+    A = G.copy()
+    A[:, :3, 3] -= np.einsum("jab,jb->ja", G[:, :3, :3], joints)
+    A[:, :3, 3] += np.array([0.0, 0.3, 0.0])
+    q = rng.normal(size=(N, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return dict(points=_t(pts), quats=_t(q), weights=_t(w), bones=_t(A))

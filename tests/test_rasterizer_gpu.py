@@ -1,0 +1,161 @@
+"""GPU parity of the sm_100a rasterizer against the UNMODIFIED reference CUDA code
+(oracle/_ref/libref_dgr.so, built from /root/reference by oracle/build_ref.sh) on identical
+synthetic inputs. Bars (BASELINE.json north_star): radii, tile keys, tile ranges, n_contrib
+bit-exact; images <= 1e-4 max-abs; gradients <= 1e-3 relative (the reference's own atomics
+are order-nondeterministic — its run-to-run noise is measured and printed next to ours)."""
+import ctypes
+
+import pytest
+import torch
+
+import refdgr
+from soar_b200 import synthetic
+from util import rel_err, run_ours, settings_of, to_device
+
+pytestmark = pytest.mark.gpu
+
+IMG_TOL = 1e-4
+GRAD_TOL = 1e-3
+
+
+def _need_ref():
+    if not refdgr.available():
+        pytest.fail("oracle/_ref/libref_dgr.so missing: run oracle/build_ref.sh where /root/reference is mounted")
+
+
+def _debug_tensors(s, out_radii):
+    """Decode our private scratch buffers through soar_rast_debug_ptr (H7)."""
+    from diff_gaussian_rasterization import _C
+    from soar_b200 import _capi
+    lib = _capi.load()
+    args = (s["bg"], s["means3D"], s.get("colors_precomp") if s.get("colors_precomp") is not None else torch.Tensor([]),
+            s["opacities"], s["scales"], s["rotations"], s["scale_modifier"], torch.Tensor([]),
+            s["viewmatrix"], s["projmatrix"], s["prcppoint"], s["patch_bbox"], s["tanfovx"], s["tanfovy"],
+            s["image_height"], s["image_width"], s["shs"] if s.get("shs") is not None else torch.Tensor([]),
+            s["sh_degree"], s["campos"], s["prefiltered"], s["render_front"], s["sort_descending"],
+            False, s["config"])
+    R, color, normal, depth, opac, radii, geom, binning, img = _C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    P, H, W = s["means3D"].shape[0], s["image_height"], s["image_width"]
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def grab(what, n, dtype):
+        p = lib.soar_rast_debug_ptr(what, P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr())
+        return refdgr._from_ptr(p, n, dtype, s["means3D"].device)
+
+    return dict(R=R, keys=grab(0, R, torch.int64), point_list=grab(1, R, torch.int32),
+                ranges=grab(2, 2 * T, torch.int32).view(T, 2), n_contrib=grab(3, H * W, torch.int32),
+                radii=radii)
+
+
+CASES = [
+    # name, P, W, H, sh_degree, surfel, bg, descending, render_front
+    ("c2_sh0_512", 100_000, 512, 512, 0, False, (0.0, 0.0, 0.0), False, False),
+    ("sh3_640x360", 60_000, 640, 360, 3, False, (1.0, 1.0, 1.0), False, False),
+    ("precomp_ragged", 30_000, 500, 333, None, False, (0.2, 0.4, 0.6), False, False),
+    ("surfel_soar", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False),
+    ("surfel_front", 50_000, 512, 512, None, True, (1.0, 1.0, 1.0), False, True),
+    ("tiny", 7, 64, 48, 1, False, (0.0, 0.0, 0.0), False, False),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_forward_backward_matches_reference(case):
+    _need_ref()
+    name, P, W, H, deg, surfel, bg, desc, front = case
+    s = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=3, surfel=surfel, bg=bg,
+                                  sort_descending=desc, render_front=front))
+    cot = to_device(synthetic.cotangents(W, H, seed=3))
+
+    ref = refdgr.RefRasterizer()
+    r_out = ref.forward(s)
+    r_g = ref.backward(cot)
+    r_g2 = ref.backward(cot)  # the reference's own atomic-order noise
+
+    out, g = run_ours(s, cot)
+    dbg = _debug_tensors(s, out["radii"])
+
+    # ---- integer contract: bit-exact ------------------------------------------------
+    assert torch.equal(out["radii"], r_out["radii"]), "radii differ"
+    assert dbg["R"] == r_out["num_rendered"], (dbg["R"], r_out["num_rendered"])
+    assert torch.equal(dbg["keys"], ref.sorted_keys()), "sorted tile|depth keys differ"
+    assert torch.equal(dbg["point_list"], ref.point_list()), "sorted Gaussian ids differ"
+    assert torch.equal(dbg["ranges"], ref.ranges()), "tile ranges differ"
+    assert torch.equal(dbg["n_contrib"], ref.n_contrib()), "n_contrib differs"
+
+    # ---- images -------------------------------------------------------------------------
+    for k in ("color", "normal", "depth", "opac"):
+        err = (out[k] - r_out[k]).abs().max().item()
+        assert err <= IMG_TOL, f"{name}: {k} max-abs {err:.3e} > {IMG_TOL}"
+
+    # ---- gradients ------------------------------------------------------------------------
+    pairs = [("means2D", "means2D"), ("means3D", "means3D"), ("opacity", "opacity"),
+             ("scales", "scales"), ("rotations", "rotations")]
+    pairs.append(("sh", "sh") if deg is not None else ("colors", "colors"))
+    report = []
+    for ours_k, ref_k in pairs:
+        a, b = g[ours_k].reshape(-1), r_g[ref_k].reshape(-1)
+        noise = rel_err(r_g2[ref_k].reshape(-1), b)
+        err = rel_err(a, b)
+        report.append(f"{ours_k}: err {err:.2e} (ref self-noise {noise:.2e})")
+        assert torch.isfinite(a).all() or not torch.isfinite(b).all(), f"{ours_k}: non-finite gradient"
+        assert err <= max(GRAD_TOL, 10 * noise), f"{name}: grad {ours_k} rel err {err:.3e}; " + "; ".join(report)
+    print(f"[{name}] R={dbg['R']} " + " | ".join(report))
+    ref.close()
+
+
+def test_empty_input():
+    s = to_device(synthetic.scene(16, 64, 64, sh_degree=0, seed=1))
+    for k in ("means3D", "shs", "opacities", "scales", "rotations"):
+        s[k] = s[k][:0]
+    out, _ = run_ours(s)
+    assert out["color"].shape == (3, 64, 64) and out["color"].abs().max().item() == 0.0
+    assert out["radii"].numel() == 0
+
+
+def test_all_culled_renders_background():
+    s = to_device(synthetic.scene(64, 96, 80, sh_degree=0, seed=2, bg=(0.25, 0.5, 0.75)))
+    s["means3D"] = s["means3D"] + torch.tensor([0.0, 0.0, 100.0], device="cuda")  # behind/outside
+    _need_ref()
+    ref = refdgr.RefRasterizer()
+    r_out = ref.forward(s)
+    out, _ = run_ours(s)
+    assert torch.equal(out["radii"], r_out["radii"])
+    for k in ("color", "normal", "depth", "opac"):
+        assert (out[k] - r_out[k]).abs().max().item() <= IMG_TOL
+    ref.close()
+
+
+def test_argument_validation_like_reference():
+    from diff_gaussian_rasterization import GaussianRasterizer
+    s = to_device(synthetic.scene(8, 32, 32, sh_degree=0, seed=1))
+    rast = GaussianRasterizer(settings_of(s))
+    m2d = torch.zeros_like(s["means3D"])
+    with pytest.raises(Exception):  # neither SHs nor colours
+        rast(s["means3D"], m2d, s["opacities"], scales=s["scales"], rotations=s["rotations"])
+    with pytest.raises(Exception):  # both scale/rot and cov3D
+        rast(s["means3D"], m2d, s["opacities"], shs=s["shs"], scales=s["scales"],
+             rotations=s["rotations"], cov3D_precomp=torch.zeros(8, 6, device="cuda"))
+    assert rast.markVisible(s["means3D"]).sum().item() == 0  # Q11: all-false
+
+
+def test_full_size_properties_c3():
+    """BASELINE config 3 (1024^2, 500k, SH3): size-independent properties — sorted keys are
+    non-decreasing, ranges partition the list, opacity in [0,1], gradients finite, and a
+    second run reproduces the integer state exactly."""
+    s = to_device(synthetic.scene(500_000, 1024, 1024, sh_degree=3, seed=0))
+    cot = to_device(synthetic.cotangents(1024, 1024, seed=0))
+    out, g = run_ours(s, cot)
+    d1 = _debug_tensors(s, out["radii"])
+    d2 = _debug_tensors(s, out["radii"])
+    assert d1["R"] == d2["R"] and torch.equal(d1["keys"], d2["keys"]) and torch.equal(d1["point_list"], d2["point_list"])
+    keys = d1["keys"]
+    assert (keys[1:] >= keys[:-1]).all(), "keys not sorted"
+    rng = d1["ranges"].long()
+    covered = (rng[:, 1] - rng[:, 0]).sum().item()
+    assert covered == d1["R"], "ranges do not partition the pair list"
+    assert out["opac"].min().item() >= 0.0 and out["opac"].max().item() <= 1.0
+    for k, v in g.items():
+        assert torch.isfinite(v).all(), f"grad {k} not finite"
+    vis = out["radii"] > 0
+    assert (g["means3D"][~vis] == 0).all(), "culled Gaussians must get zero gradient"
