@@ -156,6 +156,19 @@ int soar_lbs_backward(const float* mats, const float* quats, int32_t N, int32_t 
                       const float* dL_dout_points, const float* dL_dout_quats,
                       float* dL_dpoints, float* dL_dquats, soar_stream_t stream);
 
+/* ---- launch accounting / event timing (used by bench.py; no reference analogue:
+ *      the reference has an unused CUDA-event Timer, TS/utils/cuda_utils.cu:18-42) --- */
+/* Number of kernels this library has launched in this process. */
+unsigned long long soar_launch_count(void);
+/* on=1: start a fresh profile — every launch is bracketed by two events recorded
+ * on its own stream. on=0: stop and drop the records. */
+void soar_prof_enable(int on);
+/* Synchronises the device, then fills counts[id] / total_ms[id] for id < max_ids
+ * with the launches and summed device time seen since soar_prof_enable(1).
+ * Returns the number of kernel ids. */
+int soar_prof_summary(int max_ids, int* counts, float* total_ms);
+const char* soar_kernel_name(int id);
+
 /* ---- misc -------------------------------------------------------------------- */
 const char* soar_last_error(void);
 int soar_version(void);

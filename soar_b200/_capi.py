@@ -99,6 +99,10 @@ SIGNATURES = {
         c_int32,
         [c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "soar_launch_count": (ctypes.c_ulonglong, []),
+    "soar_prof_enable": (None, [c_int32]),
+    "soar_prof_summary": (c_int32, [c_int32, POINTER(c_int32), POINTER(c_float)]),
+    "soar_kernel_name": (c_char_p, [c_int32]),
     "soar_last_error": (c_char_p, []),
     "soar_version": (c_int32, []),
 }

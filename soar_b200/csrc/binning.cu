@@ -107,7 +107,10 @@ int launch_scan(const uint32_t* in, uint32_t* out, int n, void* status_region,
   unsigned long long* status = reinterpret_cast<unsigned long long*>(status_region);
   uint32_t* ticket = reinterpret_cast<uint32_t*>(status + n_tiles);
   (void)status_bytes;
-  scan_lookback_kernel<<<n_tiles, SCAN_THREADS, 0, stream>>>(in, out, n, status, ticket);
+  {
+    KernelScope ks(K_SCAN, stream);
+    scan_lookback_kernel<<<n_tiles, SCAN_THREADS, 0, stream>>>(in, out, n, status, ticket);
+  }
   SOAR_LAUNCH_CHECK("scan_lookback_kernel");
   return SOAR_OK;
 }
@@ -145,8 +148,11 @@ int launch_duplicate_keys(int P, const float* records, const uint32_t* tiles_tou
                           const uint32_t* offsets, unsigned long long* keys, uint32_t* values,
                           uint32_t grid_x, cudaStream_t stream) {
   if (P <= 0) return SOAR_OK;
-  duplicate_keys_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, records, tiles_touched, offsets,
-                                                              keys, values, grid_x);
+  {
+    KernelScope ks(K_DUPLICATE, stream);
+    duplicate_keys_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, records, tiles_touched, offsets,
+                                                                keys, values, grid_x);
+  }
   SOAR_LAUNCH_CHECK("duplicate_keys_kernel");
   return SOAR_OK;
 }
@@ -348,18 +354,27 @@ int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t
     return SOAR_E_WORKSPACE;
   }
   const int hist_blocks = min(tiles * 2, 148 * 8);
-  radix_hist_kernel<<<hist_blocks, 256, 0, stream>>>(keys[0], n, passes, end_bit, flip, ghist);
+  {
+    KernelScope ks(K_RADIX_HIST, stream);
+    radix_hist_kernel<<<hist_blocks, 256, 0, stream>>>(keys[0], n, passes, end_bit, flip, ghist);
+  }
   SOAR_LAUNCH_CHECK("radix_hist_kernel");
-  radix_hist_scan_kernel<<<passes, SORT_RADIX, 0, stream>>>(ghist);
+  {
+    KernelScope ks(K_RADIX_HIST_SCAN, stream);
+    radix_hist_scan_kernel<<<passes, SORT_RADIX, 0, stream>>>(ghist);
+  }
   SOAR_LAUNCH_CHECK("radix_hist_scan_kernel");
   uint32_t* tickets = status + (size_t)passes * n_sort_tiles * SORT_RADIX;
   for (int p = 0; p < passes; ++p) {
     const int shift = p * SORT_RADIX_BITS;
     const int bits = min(SORT_RADIX_BITS, end_bit - shift);
     const uint32_t mask = (1u << bits) - 1u;
-    radix_onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(
-        keys[p & 1], keys[(p + 1) & 1], values[p & 1], values[(p + 1) & 1], n, shift, mask, flip,
-        ghist + p * SORT_RADIX, status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
+    {
+      KernelScope ks(K_RADIX_ONESWEEP, stream);
+      radix_onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(
+          keys[p & 1], keys[(p + 1) & 1], values[p & 1], values[(p + 1) & 1], n, shift, mask, flip,
+          ghist + p * SORT_RADIX, status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
+    }
     SOAR_LAUNCH_CHECK("radix_onesweep_kernel");
   }
   *result_buf = passes & 1;
@@ -390,7 +405,10 @@ int launch_tile_ranges(uint32_t L, const unsigned long long* keys, uint2* ranges
                        cudaStream_t stream) {
   SOAR_CUDA_TRY(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream));
   if (L == 0) return SOAR_OK;
-  tile_ranges_kernel<<<ceil_div((int)L, 256), 256, 0, stream>>>(L, keys, ranges);
+  {
+    KernelScope ks(K_TILE_RANGES, stream);
+    tile_ranges_kernel<<<ceil_div((int)L, 256), 256, 0, stream>>>(L, keys, ranges);
+  }
   SOAR_LAUNCH_CHECK("tile_ranges_kernel");
   return SOAR_OK;
 }

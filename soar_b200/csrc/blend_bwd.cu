@@ -275,7 +275,10 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs 
 
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream) {
   dim3 grid(a.grid_x, grid_y, 1);
-  blend_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(a);
+  {
+    KernelScope ks(K_BLEND_BWD, stream);
+    blend_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(a);
+  }
   SOAR_LAUNCH_CHECK("blend_bwd_kernel");
   return SOAR_OK;
 }

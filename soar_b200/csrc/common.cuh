@@ -16,6 +16,25 @@ constexpr int TILE_PIX = TILE_X * TILE_Y;
 
 void set_error(const char* fmt, ...);
 
+// Kernel ids for launch accounting / event timing (prof.cu). Every launch site
+// opens a KernelScope right before its <<<>>>.
+enum KernelId {
+  K_PREPROCESS = 0, K_SCAN, K_DUPLICATE, K_RADIX_HIST, K_RADIX_HIST_SCAN, K_RADIX_ONESWEEP,
+  K_TILE_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_GEOM_BWD, K_KNN_BBOX, K_KNN_MORTON, K_KNN_GATHER,
+  K_KNN_BOXES, K_KNN_SEARCH, K_LBS_FWD, K_LBS_BWD, K_COUNT
+};
+
+class KernelScope {
+ public:
+  KernelScope(int id, cudaStream_t stream);
+  ~KernelScope();
+
+ private:
+  int id_;
+  cudaStream_t stream_;
+  void* e1_;
+};
+
 #define SOAR_CUDA_TRY(expr)                                                          \
   do {                                                                               \
     cudaError_t _e = (expr);                                                         \

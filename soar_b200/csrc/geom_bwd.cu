@@ -435,8 +435,14 @@ int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dcampos, 0, 3 * sizeof(float), stream));
   if (a.P <= 0) return SOAR_OK;
   const int grid = ceil_div(a.P, 256);
-  geom_bwd_kernel<false><<<grid, 256, 0, stream>>>(a);
-  geom_bwd_kernel<true><<<grid, 256, 0, stream>>>(a);
+  {
+    KernelScope ks(K_GEOM_BWD, stream);
+    geom_bwd_kernel<false><<<grid, 256, 0, stream>>>(a);
+  }
+  {
+    KernelScope ks(K_GEOM_BWD, stream);
+    geom_bwd_kernel<true><<<grid, 256, 0, stream>>>(a);
+  }
   SOAR_LAUNCH_CHECK("geom_bwd_kernel");
   return SOAR_OK;
 }

@@ -281,10 +281,19 @@ int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* work
   uint32_t* vals[2] = {reinterpret_cast<uint32_t*>(sw + L.BL.values[0]),
                        reinterpret_cast<uint32_t*>(sw + L.BL.values[1])};
 
-  knn_bbox_init_kernel<<<1, 32, 0, stream>>>(bbox);
+  {
+    KernelScope ks(K_KNN_BBOX, stream);
+    knn_bbox_init_kernel<<<1, 32, 0, stream>>>(bbox);
+  }
   const int red_blocks = min(ceil_div(P, 256), 148 * 8);
-  knn_bbox_kernel<<<red_blocks, 256, 0, stream>>>(P, points, bbox);
-  knn_morton_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, bbox, keys[0], vals[0]);
+  {
+    KernelScope ks(K_KNN_BBOX, stream);
+    knn_bbox_kernel<<<red_blocks, 256, 0, stream>>>(P, points, bbox);
+  }
+  {
+    KernelScope ks(K_KNN_MORTON, stream);
+    knn_morton_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, bbox, keys[0], vals[0]);
+  }
   SOAR_LAUNCH_CHECK("knn_morton_kernel");
   SOAR_CUDA_TRY(cudaMemsetAsync(sw + L.BL.zero_begin, 0, L.BL.zero_bytes, stream));
   int res = 0;
@@ -293,16 +302,31 @@ int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* work
                              reinterpret_cast<uint32_t*>(sw + L.BL.status), L.BL.n_sort_tiles, &res,
                              stream);
   if (rc) return rc;
-  knn_gather_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, vals[res], sorted);
-  knn_boxes_kernel<true><<<ceil_div(L.n_boxes[0] * 32, 256), 256, 0, stream>>>(
-      P, sorted, nullptr, box[0], L.n_boxes[0]);
-  knn_boxes_kernel<false><<<ceil_div(L.n_boxes[1] * 32, 256), 256, 0, stream>>>(
-      L.n_boxes[0], nullptr, box[0], box[1], L.n_boxes[1]);
-  knn_boxes_kernel<false><<<ceil_div(L.n_boxes[2] * 32, 256), 256, 0, stream>>>(
-      L.n_boxes[1], nullptr, box[1], box[2], L.n_boxes[2]);
-  knn_search_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, sorted, box[0], box[1], box[2],
-                                                          L.n_boxes[0], L.n_boxes[1],
-                                                          L.n_boxes[2], mean_dist2);
+  {
+    KernelScope ks(K_KNN_GATHER, stream);
+    knn_gather_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, vals[res], sorted);
+  }
+  {
+    KernelScope ks(K_KNN_BOXES, stream);
+    knn_boxes_kernel<true><<<ceil_div(L.n_boxes[0] * 32, 256), 256, 0, stream>>>(
+        P, sorted, nullptr, box[0], L.n_boxes[0]);
+  }
+  {
+    KernelScope ks(K_KNN_BOXES, stream);
+    knn_boxes_kernel<false><<<ceil_div(L.n_boxes[1] * 32, 256), 256, 0, stream>>>(
+        L.n_boxes[0], nullptr, box[0], box[1], L.n_boxes[1]);
+  }
+  {
+    KernelScope ks(K_KNN_BOXES, stream);
+    knn_boxes_kernel<false><<<ceil_div(L.n_boxes[2] * 32, 256), 256, 0, stream>>>(
+        L.n_boxes[1], nullptr, box[1], box[2], L.n_boxes[2]);
+  }
+  {
+    KernelScope ks(K_KNN_SEARCH, stream);
+    knn_search_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, sorted, box[0], box[1], box[2],
+                                                            L.n_boxes[0], L.n_boxes[1],
+                                                            L.n_boxes[2], mean_dist2);
+  }
   SOAR_LAUNCH_CHECK("knn_search_kernel");
   return SOAR_OK;
 }

@@ -312,8 +312,11 @@ int soar_lbs_forward(const float* weights, const float* bones, int32_t J, const 
   }
   const size_t smem = (size_t)(LBS_MAX_J * 12 + LBS_THREADS * J) * sizeof(float);
   const int grid = ceil_div(N, LBS_THREADS);
-  lbs_fwd_kernel<<<grid, LBS_THREADS, smem, stream>>>(weights, bones, J, points, quats, N,
-                                                      axis_perm, out_points, out_quats, out_mats);
+  {
+    KernelScope ks(K_LBS_FWD, stream);
+    lbs_fwd_kernel<<<grid, LBS_THREADS, smem, stream>>>(weights, bones, J, points, quats, N,
+                                                        axis_perm, out_points, out_quats, out_mats);
+  }
   SOAR_LAUNCH_CHECK("lbs_fwd_kernel");
   return SOAR_OK;
 }
@@ -328,8 +331,11 @@ int soar_lbs_backward(const float* mats, const float* quats, int32_t N, int32_t 
     set_error("soar_lbs_backward: a required pointer is NULL");
     return SOAR_E_INVALID;
   }
-  lbs_bwd_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(mats, quats, N, axis_perm, dL_dout_points,
-                                                       dL_dout_quats, dL_dpoints, dL_dquats);
+  {
+    KernelScope ks(K_LBS_BWD, stream);
+    lbs_bwd_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(mats, quats, N, axis_perm, dL_dout_points,
+                                                         dL_dout_quats, dL_dpoints, dL_dquats);
+  }
   SOAR_LAUNCH_CHECK("lbs_bwd_kernel");
   return SOAR_OK;
 }

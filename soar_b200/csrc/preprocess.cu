@@ -130,7 +130,10 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
 
 int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream) {
   if (a.P <= 0) return SOAR_OK;
-  preprocess_fwd_kernel<<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+  {
+    KernelScope ks(K_PREPROCESS, stream);
+    preprocess_fwd_kernel<<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+  }
   SOAR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return SOAR_OK;
 }

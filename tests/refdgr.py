@@ -78,7 +78,7 @@ class RefRasterizer:
     def __del__(self):
         self.close()
 
-    def forward(self, s):
+    def forward(self, s, sync=True):
         """s: scene dict of CUDA tensors (soar_b200.synthetic.scene moved to the device)."""
         dev = s["means3D"].device
         P, H, W = s["means3D"].shape[0], s["image_height"], s["image_width"]
@@ -86,7 +86,8 @@ class RefRasterizer:
         z = lambda *shape: torch.zeros(shape, dtype=torch.float32, device=dev)
         out = dict(color=z(3, H, W), normal=z(3, H, W), depth=z(1, H, W), opac=z(1, H, W),
                    radii=torch.zeros(P, dtype=torch.int32, device=dev))
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         R = self.lib.refdgr_forward(
             self.h, P, s["sh_degree"], M, _p(s["bg"]), W, H, _p(s["means3D"]), _p(s.get("shs")),
             _p(s.get("colors_precomp")), _p(s["opacities"]), _p(s.get("scales")), s["scale_modifier"],
@@ -95,13 +96,14 @@ class RefRasterizer:
             s["tanfovx"], s["tanfovy"], int(s["prefiltered"]), int(s["render_front"]),
             int(s["sort_descending"]), _p(s["config"]), _p(out["color"]), _p(out["normal"]),
             _p(out["depth"]), _p(out["opac"]), _p(out["radii"]), 0)
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         assert R >= 0, "reference forward failed"
         out["num_rendered"] = R
         self.s, self.out, self.R = s, out, R
         return out
 
-    def backward(self, cot):
+    def backward(self, cot, sync=True):
         s, dev = self.s, self.s["means3D"].device
         P, H, W = s["means3D"].shape[0], s["image_height"], s["image_width"]
         M = s["shs"].shape[1] if s.get("shs") is not None else 0
@@ -109,7 +111,8 @@ class RefRasterizer:
         g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), colors=z(P, 3), normal=z(P, 3),
                  depth=z(P, 1), means3D=z(P, 3), cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3),
                  rotations=z(P, 4), viewmat=z(4, 4), projmat=z(4, 4), campos=z(3))
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         rc = self.lib.refdgr_backward(
             self.h, P, s["sh_degree"], M, self.R, _p(s["bg"]), W, H, _p(s["means3D"]),
             _p(s.get("shs")), _p(s.get("colors_precomp")), _p(s.get("scales")), s["scale_modifier"],
@@ -120,7 +123,8 @@ class RefRasterizer:
             _p(g["colors"]), _p(g["normal"]), _p(g["depth"]), _p(g["means3D"]), _p(g["cov3D"]),
             _p(g["sh"]) if M else None, _p(g["scales"]), _p(g["rotations"]), _p(g["viewmat"]),
             _p(g["projmat"]), _p(g["campos"]), 0, _p(s["config"]))
-        torch.cuda.synchronize()
+        if sync:
+            torch.cuda.synchronize()
         assert rc == 0, "reference backward failed"
         return g
 
