@@ -355,7 +355,7 @@ def cpu_baseline(wl):
         from oracle import rast_oracle
         if not rast_oracle.available():
             raise RuntimeError("oracle/librast_oracle.so not built")
-        return rast_oracle.bench_sample(wl.name)
+        return rast_oracle.bench_sample(wl.name, wl.P, wl.W, wl.H, wl.deg, frames=2)
     except Exception as ex:  # noqa: BLE001
         return {"value": None, "unit": "frames/s", "cores": os.cpu_count(), "kind": "port",
                 "sample": f"unavailable: {ex}"}
