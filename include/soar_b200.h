@@ -93,15 +93,17 @@ size_t soar_rast_geom_bytes(int32_t P);
 size_t soar_rast_image_bytes(int32_t width, int32_t height);
 size_t soar_rast_binning_bytes(uint32_t num_rendered, int32_t width, int32_t height);
 
-/* Phase 1 (K1+K2): per-Gaussian preprocess + decoupled-look-back prefix sum of
- * tiles_touched. Writes radii[P], fills `geom`, and returns num_rendered
+/* Phase 1 (K1+K2): per-Gaussian preprocess, depth order of the Gaussians
+ * (onesweep radix sort of P depth keys) + decoupled-look-back prefix sum of
+ * tiles_touched in that order. Writes radii[P], fills `geom`, and returns num_rendered
  * through *num_rendered_host after synchronising `stream` (the reference blocks
  * at the same point, rasterizer_impl.cu:250). */
 int soar_rast_forward_bin(const SoarRastView* view, void* geom, size_t geom_bytes,
                           int32_t* radii, uint32_t* num_rendered_host, soar_stream_t stream);
 
-/* Phase 2 (K3..K6): key duplication, onesweep radix sort of tile|depth keys,
- * tile ranges, tile alpha-blend. Outputs: color[3,H,W] normal[3,H,W]
+/* Phase 2 (K3..K6): (tile, Gaussian) pair emission in depth order, stable
+ * onesweep radix sort over the tile bits, tile ranges, tile alpha-blend. The
+ * resulting list order equals the reference's sort of tile|depth keys. Outputs: color[3,H,W] normal[3,H,W]
  * depth[1,H,W] opac[1,H,W]; every pixel is written. */
 int soar_rast_forward_render(const SoarRastView* view, void* geom, void* binning,
                              size_t binning_bytes, void* img, size_t img_bytes,
@@ -127,12 +129,20 @@ int soar_rast_mark_visible(int32_t P, const float* means3D, const float* viewmat
                            const float* projmatrix, uint8_t* present, soar_stream_t stream);
 
 /* Debug accessors for parity tests: device pointers into the
- * private scratch layout. what: 0 sorted keys u64[R], 1 point_list u32[R],
+ * private scratch layout. what: 0 sorted tile ids u32[R], 1 point_list u32[R],
  * 2 ranges uint2[tiles], 3 n_contrib u32[W*H], 4 final_T f32[W*H],
- * 5 tiles_touched u32[P], 6 point_offsets u32[P], 7 records f32[P*24]. */
+ * 5 tiles_touched u32[P], 6 point_offsets u32[P] (inclusive, in depth order),
+ * 7 records f32[P*24], 8 final_D f32[W*H], 9 depth-ordered Gaussian indices u32[P]. */
 const void* soar_rast_debug_ptr(int what, int32_t P, int32_t width, int32_t height,
                                 uint32_t num_rendered, const void* geom, const void* binning,
                                 const void* img);
+/* Materialises the reference's sorted 64-bit keys (tile << 32 | depth bits,
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:66-99 after the sort at :266-285) into
+ * keys_out[R] (device). The product never builds them: it sorts Gaussians by
+ * depth once and the (tile, index) pairs by tile only. */
+int soar_rast_debug_sorted_keys(int32_t P, int32_t width, int32_t height, uint32_t num_rendered,
+                                const void* geom, const void* binning, uint64_t* keys_out,
+                                soar_stream_t stream);
 
 /* ---- KNN (replaces `simple_knn._C.distCUDA2`, KNN/ext.cpp:15-17 ->
  *      SimpleKNN::knn, KNN/simple_knn.cu:186-222) ------------------------------- */

@@ -88,6 +88,10 @@ SIGNATURES = {
         c_void_p,
         [c_int32, c_int32, c_int32, c_int32, c_uint32, c_void_p, c_void_p, c_void_p],
     ),
+    "soar_rast_debug_sorted_keys": (
+        c_int32,
+        [c_int32, c_int32, c_int32, c_uint32, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "soar_knn_workspace_bytes": (c_size_t, [c_int32]),
     "soar_knn_dist2": (c_int32, [c_void_p, c_int32, c_void_p, c_void_p, c_size_t, c_void_p]),
     "soar_lbs_forward": (

@@ -27,15 +27,15 @@ static inline const char* at(const void* base, size_t off) {
 }
 
 struct ViewDims {
-  int grid_x, grid_y, n_tiles, sort_bits, passes;
+  int grid_x, grid_y, n_tiles, tile_bits, passes;  // passes of the tile-id sort
 };
 static inline ViewDims view_dims(int W, int H) {
   ViewDims d;
   d.grid_x = ceil_div(W, TILE_X);
   d.grid_y = ceil_div(H, TILE_Y);
   d.n_tiles = d.grid_x * d.grid_y;
-  d.sort_bits = 32 + tile_id_bits((uint32_t)d.n_tiles);
-  d.passes = sort_passes(d.sort_bits);
+  d.tile_bits = tile_id_bits((uint32_t)d.n_tiles);
+  d.passes = sort_passes(d.tile_bits);
   return d;
 }
 
@@ -113,10 +113,14 @@ int soar_rast_forward_bin(const SoarRastView* v, void* geom, size_t geom_bytes, 
   }
   const ViewDims d = view_dims(v->width, v->height);
 
-  SOAR_CUDA_TRY(cudaMemsetAsync(at(geom, L.scan_status), 0, L.scan_status_bytes, stream));
+  SOAR_CUDA_TRY(cudaMemsetAsync(at(geom, L.zero_begin), 0, L.zero_bytes, stream));
   const int n_scan_tiles = ceil_div(v->P, SCAN_TILE);
   uint32_t* tail = reinterpret_cast<uint32_t*>(at(geom, L.scan_status) +
                                                (size_t)n_scan_tiles * sizeof(uint64_t));
+  uint32_t* dkeys[2] = {reinterpret_cast<uint32_t*>(at(geom, L.depth_keys[0])),
+                        reinterpret_cast<uint32_t*>(at(geom, L.depth_keys[1]))};
+  uint32_t* perm[2] = {reinterpret_cast<uint32_t*>(at(geom, L.perm[0])),
+                       reinterpret_cast<uint32_t*>(at(geom, L.perm[1]))};
   PreprocessArgs a;
   a.P = v->P; a.D = v->sh_degree; a.M = v->M; a.W = v->width; a.H = v->height;
   a.tanfovx = v->tanfovx; a.tanfovy = v->tanfovy;
@@ -133,12 +137,20 @@ int soar_rast_forward_bin(const SoarRastView* v, void* geom, size_t geom_bytes, 
   a.radii = radii;
   a.records = reinterpret_cast<float*>(at(geom, L.records));
   a.tiles_touched = reinterpret_cast<uint32_t*>(at(geom, L.tiles_touched));
+  a.depth_keys = dkeys[0];
   a.error_flag = tail + 1;
   rc = launch_preprocess_fwd(a, stream);
   if (rc) return rc;
+  // depth order of the Gaussians (stable: ties stay in index order); 4 passes -> buffer 0
+  int dsorted = 0;
+  rc = launch_radix_sort(dkeys, perm, (uint32_t)v->P, 32, v->sort_descending != 0,
+                         /*iota_values=*/true, /*have_hist=*/false,
+                         reinterpret_cast<uint32_t*>(at(geom, L.ghist)),
+                         reinterpret_cast<uint32_t*>(at(geom, L.sort_status)), L.n_sort_tiles,
+                         &dsorted, stream);
+  if (rc) return rc;
   uint32_t* offsets = reinterpret_cast<uint32_t*>(at(geom, L.point_offsets));
-  rc = launch_scan(a.tiles_touched, offsets, v->P, at(geom, L.scan_status), L.scan_status_bytes,
-                   stream);
+  rc = launch_scan(a.tiles_touched, perm[dsorted], offsets, v->P, at(geom, L.scan_status), stream);
   if (rc) return rc;
   // the one host sync of the forward (reference: rasterizer_impl.cu:250)
   uint32_t flag = 0;
@@ -180,21 +192,23 @@ int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
   const GeomLayout GL = geom_layout(v->P);
   const float* records = reinterpret_cast<const float*>(at(geom, GL.records));
 
-  unsigned long long* keys[2] = {reinterpret_cast<unsigned long long*>(at(binning, BL.keys[0])),
-                                 reinterpret_cast<unsigned long long*>(at(binning, BL.keys[1]))};
+  uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(at(binning, BL.keys[0])),
+                       reinterpret_cast<uint32_t*>(at(binning, BL.keys[1]))};
   uint32_t* values[2] = {reinterpret_cast<uint32_t*>(at(binning, BL.values[0])),
                          reinterpret_cast<uint32_t*>(at(binning, BL.values[1]))};
   uint2* ranges = reinterpret_cast<uint2*>(at(img, IL.ranges));
   int sorted = 0;
   if (num_rendered > 0) {
     SOAR_CUDA_TRY(cudaMemsetAsync(at(binning, BL.zero_begin), 0, BL.zero_bytes, stream));
-    rc = launch_duplicate_keys(v->P, records,
-                               reinterpret_cast<const uint32_t*>(at(geom, GL.tiles_touched)),
-                               reinterpret_cast<const uint32_t*>(at(geom, GL.point_offsets)),
-                               keys[0], values[0], d.grid_x, stream);
+    uint32_t* ghist = reinterpret_cast<uint32_t*>(at(binning, BL.ghist));
+    rc = launch_duplicate_tiles(v->P, records,
+                                reinterpret_cast<const uint32_t*>(at(geom, GL.perm[0])),
+                                reinterpret_cast<const uint32_t*>(at(geom, GL.point_offsets)),
+                                keys[0], values[0], d.grid_x, v->sort_descending != 0, d.tile_bits,
+                                ghist, stream);
     if (rc) return rc;
-    rc = launch_radix_sort(keys, values, num_rendered, d.sort_bits, v->sort_descending != 0,
-                           reinterpret_cast<uint32_t*>(at(binning, BL.ghist)),
+    rc = launch_radix_sort(keys, values, num_rendered, d.tile_bits, v->sort_descending != 0,
+                           /*iota_values=*/false, /*have_hist=*/true, ghist,
                            reinterpret_cast<uint32_t*>(at(binning, BL.status)), BL.n_sort_tiles,
                            &sorted, stream);
     if (rc) return rc;
@@ -298,7 +312,7 @@ const void* soar_rast_debug_ptr(int what, int32_t P, int32_t width, int32_t heig
   const BinningLayout BL = binning_layout(num_rendered, d.passes);
   const int sorted = num_rendered > 0 ? (d.passes & 1) : 0;
   switch (what) {
-    case 0: return binning ? at(binning, BL.keys[sorted]) : nullptr;
+    case 0: return binning ? at(binning, BL.keys[sorted]) : nullptr;  // u32 tile ids
     case 1: return binning ? at(binning, BL.values[sorted]) : nullptr;
     case 2: return img ? at(img, IL.ranges) : nullptr;
     case 3: return img ? at(img, IL.n_contrib) : nullptr;
@@ -307,8 +321,24 @@ const void* soar_rast_debug_ptr(int what, int32_t P, int32_t width, int32_t heig
     case 6: return geom ? at(geom, GL.point_offsets) : nullptr;
     case 7: return geom ? at(geom, GL.records) : nullptr;
     case 8: return img ? at(img, IL.final_D) : nullptr;
+    case 9: return geom ? at(geom, GL.perm[0]) : nullptr;
   }
   return nullptr;
+}
+
+int soar_rast_debug_sorted_keys(int32_t P, int32_t width, int32_t height, uint32_t num_rendered,
+                                const void* geom, const void* binning, uint64_t* keys_out,
+                                soar_stream_t stream_) {
+  if (num_rendered == 0) return SOAR_OK;
+  if (!geom || !binning || !keys_out) { set_error("debug_sorted_keys: NULL pointer"); return SOAR_E_INVALID; }
+  const ViewDims d = view_dims(width, height);
+  const GeomLayout GL = geom_layout(P);
+  const BinningLayout BL = binning_layout(num_rendered, d.passes);
+  const int sorted = d.passes & 1;
+  return launch_debug_keys(num_rendered, reinterpret_cast<const uint32_t*>(at(binning, BL.keys[sorted])),
+                           reinterpret_cast<const uint32_t*>(at(binning, BL.values[sorted])),
+                           reinterpret_cast<const float*>(at(geom, GL.records)),
+                           reinterpret_cast<unsigned long long*>(keys_out), (cudaStream_t)stream_);
 }
 
 }  // extern "C"

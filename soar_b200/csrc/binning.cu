@@ -1,13 +1,24 @@
-// K2..K5 — binning for sm_100a:
-//   * single-pass decoupled look-back inclusive scan of tiles_touched
-//     (replaces cub::DeviceScan::InclusiveSum, DGR rasterizer_impl.cu:242-245);
-//   * key duplication, key = tile_id << 32 | depth bits (rasterizer_impl.cu:66-99);
-//   * in-house onesweep LSD radix sort of (u64 key, u32 value) pairs — one
-//     histogram pass for all digit places, then one chained-scan scatter pass per
-//     8-bit digit with per-digit decoupled look-back (replaces
-//     cub::DeviceRadixSort::SortPairs[Descending], rasterizer_impl.cu:266-285);
-//     stable, ascending or descending over bits [0, end_bit);
-//   * tile ranges from the sorted keys (rasterizer_impl.cu:104-124).
+// K2..K5 — binning for sm_100a.
+//
+// The reference (DGR/cuda_rasterizer/rasterizer_impl.cu:242-295) scans
+// tiles_touched, writes one 64-bit key (tile << 32 | depth bits) per (Gaussian,
+// tile) pair in Gaussian order, radix-sorts all R pairs over 32+b bits (6 byte
+// passes at 1024^2) and finds the tile ranges. The sorted order it defines is
+//      (tile, depth bits, Gaussian index)           [stable LSD sort, unique
+//                                                    (Gaussian, tile) pairs]
+// and that order — not the way it is reached — is the contract we are compared
+// against bit for bit. Here it is reached with far less traffic:
+//   1. the P Gaussians are sorted by depth bits ONCE (stable, so ties stay in
+//      index order): 4 byte passes over P 8-byte pairs instead of over R pairs;
+//   2. a decoupled look-back scan of tiles_touched in that order gives every
+//      Gaussian its slot range;
+//   3. pairs are emitted in depth order by warps that write whole contiguous
+//      runs (coalesced), with a 32-bit key that is just the tile id; the digit
+//      histograms of the tile sort are accumulated on the fly;
+//   4. a stable onesweep sort over the b tile bits only (2 byte passes at
+//      1024^2) of 8-byte pairs puts the pairs in (tile, depth, index) order;
+//   5. tile ranges are read off the sorted tile ids.
+// Descending order (SOAR's back-normal view, sort_descending) flips both sorts.
 // All of it is integer/byte work bound by HBM traffic; nothing here is shaped
 // for tensor cores.
 #include "common.cuh"
@@ -18,14 +29,16 @@ namespace soar {
 
 // =================================================================================
 // Inclusive scan, decoupled look-back. status word: [63:62] flag, [31:0] value.
+// Optional gather: element k is in[index[k]].
 // =================================================================================
 constexpr unsigned long long SCAN_FLAG_AGG = 1ull << 62;
 constexpr unsigned long long SCAN_FLAG_INCL = 2ull << 62;
 constexpr unsigned long long SCAN_FLAG_MASK = 3ull << 62;
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_lookback_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
-                     unsigned long long* status, uint32_t* ticket) {
+scan_lookback_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict__ index,
+                     uint32_t* __restrict__ out, int n, unsigned long long* status,
+                     uint32_t* ticket) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_warp[SCAN_THREADS / 32];
   __shared__ uint32_t s_prefix;
@@ -36,7 +49,17 @@ scan_lookback_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out
   const int base = tile * SCAN_TILE + tid * SCAN_ITEMS;
 
   uint32_t v[SCAN_ITEMS];
-  if (base + SCAN_ITEMS <= n) {
+  if (index != nullptr) {
+    if (base + SCAN_ITEMS <= n) {
+      const uint4* p = reinterpret_cast<const uint4*>(index + base);
+      const uint4 a = p[0], b = p[1];
+      v[0] = in[a.x]; v[1] = in[a.y]; v[2] = in[a.z]; v[3] = in[a.w];
+      v[4] = in[b.x]; v[5] = in[b.y]; v[6] = in[b.z]; v[7] = in[b.w];
+    } else {
+#pragma unroll
+      for (int i = 0; i < SCAN_ITEMS; ++i) v[i] = (base + i < n) ? in[index[base + i]] : 0u;
+    }
+  } else if (base + SCAN_ITEMS <= n) {
     const uint4* p = reinterpret_cast<const uint4*>(in + base);
     uint4 a = p[0], b = p[1];
     v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
@@ -99,66 +122,123 @@ scan_lookback_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out
   }
 }
 
-int launch_scan(const uint32_t* in, uint32_t* out, int n, void* status_region,
-                size_t status_bytes, cudaStream_t stream) {
+int launch_scan(const uint32_t* in, const uint32_t* index, uint32_t* out, int n,
+                void* status_region, cudaStream_t stream) {
   if (n <= 0) return SOAR_OK;
   const int n_tiles = ceil_div(n, SCAN_TILE);
   // region layout: u64 status[n_tiles] | u32 ticket | u32 error flag (zeroed by caller)
   unsigned long long* status = reinterpret_cast<unsigned long long*>(status_region);
   uint32_t* ticket = reinterpret_cast<uint32_t*>(status + n_tiles);
-  (void)status_bytes;
   {
     KernelScope ks(K_SCAN, stream);
-    scan_lookback_kernel<<<n_tiles, SCAN_THREADS, 0, stream>>>(in, out, n, status, ticket);
+    scan_lookback_kernel<<<n_tiles, SCAN_THREADS, 0, stream>>>(in, index, out, n, status, ticket);
   }
   SOAR_LAUNCH_CHECK("scan_lookback_kernel");
   return SOAR_OK;
 }
 
 // =================================================================================
-// Key duplication
+// Pair emission in depth order. One warp owns 32 consecutive Gaussians of the
+// depth-sorted permutation; their slot ranges are contiguous, so the warp writes
+// one contiguous run of (tile id, Gaussian index) pairs, 32 at a time, each lane
+// finding the owner of its slot with a 5-step search over the lanes' start
+// offsets. Row-major over the tile rect like rasterizer_impl.cu:88-97.
+// The digit histograms of the tile sort are accumulated here (no extra pass).
 // =================================================================================
-__global__ void __launch_bounds__(256)
-duplicate_keys_kernel(int P, const float* __restrict__ records,
-                      const uint32_t* __restrict__ tiles_touched,
-                      const uint32_t* __restrict__ offsets, unsigned long long* __restrict__ keys,
-                      uint32_t* __restrict__ values, uint32_t grid_x) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
-  if (tiles_touched[idx] == 0) return;
-  uint32_t off = (idx == 0) ? 0u : offsets[idx - 1];
-  const float4 r1 = reinterpret_cast<const float4*>(records + (size_t)idx * REC_FLOATS)[1];
-  const float4 r5 = reinterpret_cast<const float4*>(records + (size_t)idx * REC_FLOATS)[5];
-  const uint32_t depth_bits = __float_as_uint(r1.z);
-  const uint32_t rx = __float_as_uint(r5.x), ry = __float_as_uint(r5.y);
-  const uint32_t x0 = rx & 0xffffu, x1 = rx >> 16, y0 = ry & 0xffffu, y1 = ry >> 16;
-  for (uint32_t y = y0; y < y1; ++y) {
-    for (uint32_t x = x0; x < x1; ++x) {
-      unsigned long long key = (unsigned long long)(y * grid_x + x);
-      key <<= 32;
-      key |= depth_bits;
-      keys[off] = key;
-      values[off] = (uint32_t)idx;
-      ++off;
+constexpr int DUP_THREADS = 256;
+
+__global__ void __launch_bounds__(DUP_THREADS)
+duplicate_tiles_kernel(int P, const float* __restrict__ records, const uint32_t* __restrict__ perm,
+                       const uint32_t* __restrict__ offsets_incl, uint32_t* __restrict__ keys,
+                       uint32_t* __restrict__ values, uint32_t grid_x, uint32_t flip, int passes,
+                       int end_bit, uint32_t* __restrict__ ghist) {
+  __shared__ uint32_t s_hist[SORT_MAX_PASSES_R * SORT_RADIX];
+  for (int i = threadIdx.x; i < passes * SORT_RADIX; i += DUP_THREADS) s_hist[i] = 0;
+  __syncthreads();
+
+  const uint32_t lane = lane_id();
+  const int k = blockIdx.x * DUP_THREADS + threadIdx.x;
+  uint32_t idx = 0, start = 0, tt = 0, xy0 = 0, w = 1;
+  if (k < P) {
+    idx = perm[k];
+    const uint32_t incl = offsets_incl[k];
+    const uint32_t prev = (k == 0) ? 0u : offsets_incl[k - 1];
+    tt = incl - prev;
+    start = prev;
+    if (tt != 0) {
+      const float4 r5 = __ldg(reinterpret_cast<const float4*>(records + (size_t)idx * REC_FLOATS) + 5);
+      const uint32_t rx = __float_as_uint(r5.x), ry = __float_as_uint(r5.y);
+      xy0 = (rx & 0xffffu) | (ry << 16);
+      w = (rx >> 16) - (rx & 0xffffu);
     }
+  } else {
+    // pad lanes: start at the end of the warp's run so the search never selects them early
+    start = 0xffffffffu;
+  }
+  const uint32_t run_begin = __shfl_sync(0xffffffffu, start, 0);
+  // end of the run = start + tt of the last valid lane
+  uint32_t endv = (k < P) ? start + tt : 0u;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) endv = max(endv, __shfl_xor_sync(0xffffffffu, endv, o));
+  const uint32_t run_end = endv;
+
+  for (uint32_t slot0 = run_begin; slot0 < run_end; slot0 += 32) {
+    const uint32_t slot = slot0 + lane;
+    // owner = last lane whose start <= slot (zero-size lanes are skipped by "last")
+    uint32_t j = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const uint32_t cand = j + step;
+      const uint32_t v = __shfl_sync(0xffffffffu, start, cand & 31);
+      if (v <= slot) j = cand;
+    }
+    const uint32_t o_start = __shfl_sync(0xffffffffu, start, j);
+    const uint32_t o_xy0 = __shfl_sync(0xffffffffu, xy0, j);
+    const uint32_t o_w = __shfl_sync(0xffffffffu, w, j);
+    const uint32_t o_idx = __shfl_sync(0xffffffffu, idx, j);
+    if (slot < run_end) {
+      const uint32_t r = slot - o_start;
+      const uint32_t row = r / o_w, col = r - row * o_w;
+      const uint32_t tile = ((o_xy0 >> 16) + row) * grid_x + (o_xy0 & 0xffffu) + col;
+      keys[slot] = tile;
+      values[slot] = o_idx;
+      const uint32_t kf = tile ^ flip;
+      for (int p = 0; p < passes; ++p) {
+        const int shift = p * SORT_RADIX_BITS;
+        const int bits = min(SORT_RADIX_BITS, end_bit - shift);
+        atomicAdd(&s_hist[p * SORT_RADIX + ((kf >> shift) & ((1u << bits) - 1u))], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * SORT_RADIX; i += DUP_THREADS) {
+    const uint32_t c = s_hist[i];
+    if (c) atomicAdd(&ghist[i], c);
   }
 }
 
-int launch_duplicate_keys(int P, const float* records, const uint32_t* tiles_touched,
-                          const uint32_t* offsets, unsigned long long* keys, uint32_t* values,
-                          uint32_t grid_x, cudaStream_t stream) {
+int launch_duplicate_tiles(int P, const float* records, const uint32_t* perm,
+                           const uint32_t* offsets_incl, uint32_t* keys, uint32_t* values,
+                           uint32_t grid_x, bool descending, int tile_bits, uint32_t* ghist,
+                           cudaStream_t stream) {
   if (P <= 0) return SOAR_OK;
+  const int passes = sort_passes(tile_bits);
+  if (passes > SORT_MAX_PASSES_R) {
+    set_error("duplicate: %d tile bits need more than %d passes", tile_bits, SORT_MAX_PASSES_R);
+    return SOAR_E_INVALID;
+  }
   {
     KernelScope ks(K_DUPLICATE, stream);
-    duplicate_keys_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, records, tiles_touched, offsets,
-                                                                keys, values, grid_x);
+    duplicate_tiles_kernel<<<ceil_div(P, DUP_THREADS), DUP_THREADS, 0, stream>>>(
+        P, records, perm, offsets_incl, keys, values, grid_x, descending ? 0xffffffffu : 0u, passes,
+        tile_bits, ghist);
   }
-  SOAR_LAUNCH_CHECK("duplicate_keys_kernel");
+  SOAR_LAUNCH_CHECK("duplicate_tiles_kernel");
   return SOAR_OK;
 }
 
 // =================================================================================
-// Onesweep radix sort
+// Onesweep radix sort of (u32 key, u32 value) pairs
 // =================================================================================
 constexpr uint32_t RS_FLAG_AGG = 1u << 30;
 constexpr uint32_t RS_FLAG_INCL = 2u << 30;
@@ -167,18 +247,18 @@ constexpr uint32_t RS_VALUE_MASK = (1u << 30) - 1u;
 
 // One pass over the keys builds the digit histograms of every pass.
 __global__ void __launch_bounds__(256)
-radix_hist_kernel(const unsigned long long* __restrict__ keys, uint32_t n, int passes, int end_bit,
-                  unsigned long long flip, uint32_t* __restrict__ ghist) {
+radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int passes, int end_bit,
+                  uint32_t flip, uint32_t* __restrict__ ghist) {
   __shared__ uint32_t sh[SORT_MAX_PASSES * SORT_RADIX];
   for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) sh[i] = 0;
   __syncthreads();
   const uint32_t stride = gridDim.x * blockDim.x;
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const unsigned long long k = keys[i] ^ flip;
+    const uint32_t k = keys[i] ^ flip;
     for (int p = 0; p < passes; ++p) {
       const int shift = p * SORT_RADIX_BITS;
       const int bits = min(SORT_RADIX_BITS, end_bit - shift);
-      const uint32_t d = (uint32_t)(k >> shift) & ((1u << bits) - 1u);
+      const uint32_t d = (k >> shift) & ((1u << bits) - 1u);
       atomicAdd(&sh[p * SORT_RADIX + d], 1u);
     }
   }
@@ -208,14 +288,13 @@ __global__ void __launch_bounds__(SORT_RADIX) radix_hist_scan_kernel(uint32_t* g
   h[tid] = off + incl - c;
 }
 
+// vals_in == nullptr: the value of element i is i (first pass of the depth sort).
 __global__ void __launch_bounds__(SORT_THREADS)
-radix_onesweep_kernel(const unsigned long long* __restrict__ keys_in,
-                      unsigned long long* __restrict__ keys_out,
+radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                       const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                      uint32_t n, int shift, uint32_t digit_mask, unsigned long long flip,
-                      const uint32_t* __restrict__ ghist_excl, uint32_t* status,
-                      uint32_t* ticket) {
-  __shared__ unsigned long long s_keys[SORT_TILE];
+                      uint32_t n, int shift, uint32_t digit_mask, uint32_t flip,
+                      const uint32_t* __restrict__ ghist_excl, uint32_t* status, uint32_t* ticket) {
+  __shared__ uint32_t s_keys[SORT_TILE];
   __shared__ uint32_t s_vals[SORT_TILE];
   __shared__ uint32_t s_warp_hist[SORT_THREADS / 32][SORT_RADIX];
   __shared__ uint32_t s_gofs[SORT_RADIX];
@@ -234,18 +313,18 @@ radix_onesweep_kernel(const unsigned long long* __restrict__ keys_in,
   const uint32_t n_valid = min((uint32_t)SORT_TILE, n - tile_base);
 
   // ---- load (warp-striped inside each warp's contiguous chunk) and rank ----------
-  unsigned long long key[SORT_ITEMS];
+  uint32_t key[SORT_ITEMS];
   uint32_t rank[SORT_ITEMS];
   const uint32_t warp_base = warp * (32 * SORT_ITEMS);
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
     const uint32_t local = warp_base + j * 32 + lane;
-    key[j] = (local < n_valid) ? keys_in[tile_base + local] : (~0ull ^ flip);
+    key[j] = (local < n_valid) ? keys_in[tile_base + local] : (~0u ^ flip);
   }
   const uint32_t lt_mask = lanemask_lt();
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
-    const uint32_t d = (uint32_t)((key[j] ^ flip) >> shift) & digit_mask;
+    const uint32_t d = ((key[j] ^ flip) >> shift) & digit_mask;
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const uint32_t lt = __popc(peers & lt_mask);
     const uint32_t pre = s_warp_hist[warp][d];
@@ -306,7 +385,7 @@ radix_onesweep_kernel(const unsigned long long* __restrict__ keys_in,
   // ---- exchange through shared memory so the global scatter is run-coalesced -----
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
-    const uint32_t d = (uint32_t)((key[j] ^ flip) >> shift) & digit_mask;
+    const uint32_t d = ((key[j] ^ flip) >> shift) & digit_mask;
     const uint32_t pos = s_digit_excl[d] + s_warp_hist[warp][d] + rank[j];
     rank[j] = pos;
     s_keys[pos] = key[j];
@@ -314,15 +393,15 @@ radix_onesweep_kernel(const unsigned long long* __restrict__ keys_in,
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
     const uint32_t local = warp_base + j * 32 + lane;
-    if (local < n_valid) s_vals[rank[j]] = vals_in[tile_base + local];
+    if (local < n_valid) s_vals[rank[j]] = vals_in ? vals_in[tile_base + local] : tile_base + local;
   }
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < SORT_ITEMS; ++i) {
     const uint32_t p = i * SORT_THREADS + tid;
     if (p < n_valid) {
-      const unsigned long long k = s_keys[p];
-      const uint32_t d = (uint32_t)((k ^ flip) >> shift) & digit_mask;
+      const uint32_t k = s_keys[p];
+      const uint32_t d = ((k ^ flip) >> shift) & digit_mask;
       const uint32_t dst = s_gofs[d] + p;
       keys_out[dst] = k;
       vals_out[dst] = s_vals[p];
@@ -330,12 +409,14 @@ radix_onesweep_kernel(const unsigned long long* __restrict__ keys_in,
   }
 }
 
-// Sort `n` pairs by key bits [0, end_bit). Input in keys[0]/values[0]; returns the
-// index (0/1) of the buffer pair holding the result through *result_buf.
-// `ghist` (SORT_MAX_PASSES*256 u32) and `status` must be zero on entry.
-int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t n, int end_bit,
-                      bool descending, uint32_t* ghist, uint32_t* status, int n_sort_tiles,
-                      int* result_buf, cudaStream_t stream) {
+// Stable sort of `n` (u32 key, u32 value) pairs by key bits [0, end_bit). Input in
+// keys[0]/values[0] (values[0] may be implied = element index when iota_values);
+// *result_buf = index (0/1) of the buffer pair holding the result.
+// `ghist` (passes*256 u32) must hold the digit COUNTS when have_hist, else zeros;
+// `status` must be zero on entry.
+int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int end_bit,
+                      bool descending, bool iota_values, bool have_hist, uint32_t* ghist,
+                      uint32_t* status, int n_sort_tiles, int* result_buf, cudaStream_t stream) {
   *result_buf = 0;
   if (n == 0 || end_bit <= 0) return SOAR_OK;
   const int passes = sort_passes(end_bit);
@@ -347,14 +428,14 @@ int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t
     set_error("radix sort: %u pairs exceed the 2^30 look-back counter range", n);
     return SOAR_E_INVALID;
   }
-  const unsigned long long flip = descending ? ~0ull : 0ull;
+  const uint32_t flip = descending ? ~0u : 0u;
   const int tiles = ceil_div((int)n, SORT_TILE);
   if (tiles > n_sort_tiles) {
     set_error("radix sort: status region sized for %d tiles, need %d", n_sort_tiles, tiles);
     return SOAR_E_WORKSPACE;
   }
-  const int hist_blocks = min(tiles * 2, 148 * 8);
-  {
+  if (!have_hist) {
+    const int hist_blocks = min(tiles * 2, 148 * 8);
     KernelScope ks(K_RADIX_HIST, stream);
     radix_hist_kernel<<<hist_blocks, 256, 0, stream>>>(keys[0], n, passes, end_bit, flip, ghist);
   }
@@ -372,8 +453,9 @@ int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t
     {
       KernelScope ks(K_RADIX_ONESWEEP, stream);
       radix_onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(
-          keys[p & 1], keys[(p + 1) & 1], values[p & 1], values[(p + 1) & 1], n, shift, mask, flip,
-          ghist + p * SORT_RADIX, status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
+          keys[p & 1], keys[(p + 1) & 1], (p == 0 && iota_values) ? nullptr : values[p & 1],
+          values[(p + 1) & 1], n, shift, mask, flip, ghist + p * SORT_RADIX,
+          status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
     }
     SOAR_LAUNCH_CHECK("radix_onesweep_kernel");
   }
@@ -382,17 +464,17 @@ int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t
 }
 
 // =================================================================================
-// Tile ranges
+// Tile ranges (rasterizer_impl.cu:104-124) from the sorted tile ids
 // =================================================================================
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(uint32_t L, const unsigned long long* __restrict__ keys, uint2* ranges) {
+tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= L) return;
-  const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+  const uint32_t cur = keys[idx];
   if (idx == 0) {
     ranges[cur].x = 0;
   } else {
-    const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+    const uint32_t prev = keys[idx - 1];
     if (cur != prev) {
       ranges[prev].y = idx;
       ranges[cur].x = idx;
@@ -401,7 +483,7 @@ tile_ranges_kernel(uint32_t L, const unsigned long long* __restrict__ keys, uint
   if (idx == L - 1) ranges[cur].y = L;
 }
 
-int launch_tile_ranges(uint32_t L, const unsigned long long* keys, uint2* ranges, int n_tiles,
+int launch_tile_ranges(uint32_t L, const uint32_t* keys, uint2* ranges, int n_tiles,
                        cudaStream_t stream) {
   SOAR_CUDA_TRY(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream));
   if (L == 0) return SOAR_OK;
@@ -410,6 +492,27 @@ int launch_tile_ranges(uint32_t L, const unsigned long long* keys, uint2* ranges
     tile_ranges_kernel<<<ceil_div((int)L, 256), 256, 0, stream>>>(L, keys, ranges);
   }
   SOAR_LAUNCH_CHECK("tile_ranges_kernel");
+  return SOAR_OK;
+}
+
+// =================================================================================
+// Debug: materialise the reference's 64-bit keys (tile << 32 | depth bits) of the
+// sorted list, for the bit-exact parity tests.
+// =================================================================================
+__global__ void __launch_bounds__(256)
+debug_keys_kernel(uint32_t L, const uint32_t* __restrict__ tiles, const uint32_t* __restrict__ ids,
+                  const float* __restrict__ records, unsigned long long* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= L) return;
+  const float depth = records[(size_t)ids[i] * REC_FLOATS + REC_DEPTH];
+  out[i] = ((unsigned long long)tiles[i] << 32) | __float_as_uint(depth);
+}
+
+int launch_debug_keys(uint32_t L, const uint32_t* tiles, const uint32_t* ids, const float* records,
+                      unsigned long long* out, cudaStream_t stream) {
+  if (L == 0) return SOAR_OK;
+  debug_keys_kernel<<<ceil_div((int)L, 256), 256, 0, stream>>>(L, tiles, ids, records, out);
+  SOAR_LAUNCH_CHECK("debug_keys_kernel");
   return SOAR_OK;
 }
 

@@ -5,22 +5,26 @@
 // the same 13 partial derivatives as the reference are formed (colour 3,
 // normal 3 (x10, Q4), depth 1, mean2D 2, conic 3, opacity 1).
 //
-// What is ours: the reference issues 13 global atomicAdds per (pixel, Gaussian)
-// contribution. Here the 13 values are reduced across the 32 pixels of a warp
-// with a transposed butterfly (16 shuffles for all 13 values together, not 5
-// per value), the 8 warps of the tile meet in a shared-memory accumulator, and
-// the tile flushes ONE set of (vectorised) global reductions per Gaussian per
-// batch into a 64-byte per-Gaussian accumulator. Warps in which no pixel sees
-// the Gaussian skip the reduction with one vote; the replay starts at the
-// tile's deepest n_contrib instead of the end of the tile's range.
+// What is ours:
+//   * the reference issues 13 global atomicAdds per (pixel, Gaussian) contribution. Here
+//     the 13 values are reduced across the 32 pixels of a warp with a transposed butterfly
+//     (16 shuffles for all 13 values together, not 5 per value), the 8 warps of the tile
+//     meet in a shared-memory accumulator, and the tile flushes ONE set of vectorised
+//     global reductions per Gaussian per batch into a 64-byte per-Gaussian accumulator;
+//   * the replay starts at the tile's deepest n_contrib instead of the end of its range;
+//   * list entries that cannot reach alpha >= 1/255 anywhere in the tile are dropped at
+//     staging time, and every warp (an 8x4 pixel block) only visits the entries whose
+//     footprint can touch its block (blend_common.cuh);
+//   * pixel-constant factors are hoisted, 1/(1-alpha) is formed once per contribution, and
+//     the body is specialised on (surface, per-pixel depth, normalize_depth).
 #include "common.cuh"
 #include "layout.h"
 #include "kernels.h"
+#include "blend_common.cuh"
 
 namespace soar {
 
 constexpr int BWD_BATCH = TILE_PIX;
-
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
@@ -68,35 +72,38 @@ __device__ __forceinline__ float warp_reduce16(float (&v)[16], uint32_t lane) {
   return v[0];
 }
 
-__global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs a) {
-  __shared__ float4 s_q0[BWD_BATCH];  // x y conA conB
-  __shared__ float4 s_q1[BWD_BATCH];  // conC opac depth J6
-  __shared__ float4 s_q2[BWD_BATCH];  // r g b J9
-  __shared__ float4 s_q3[BWD_BATCH];  // nx ny nz -
-  __shared__ float4 s_q4[BWD_BATCH];  // J0 J1 J2 J3
-  __shared__ uint32_t s_id[BWD_BATCH];
-  __shared__ float s_acc[BWD_BATCH][GACC_FLOATS];
-  __shared__ uint32_t s_max_contrib[TILE_PIX / 32];
+struct BlendBwdSmem {
+  float4 q0[BWD_BATCH];  // x y conA conB
+  float4 q1[BWD_BATCH];  // conC opac thr depth
+  float4 q2[BWD_BATCH];  // r g b J6
+  float4 q3[BWD_BATCH];  // nx ny nz J9
+  float4 q4[BWD_BATCH];  // J0 J1 J2 J3
+  uint32_t id[BWD_BATCH];
+  uint32_t pos[BWD_BATCH];  // 0-based position in the tile's list
+  uint8_t mask[BWD_BATCH];
+  float acc[BWD_BATCH][GACC_FLOATS];
+  uint32_t wcount[N_BLK];
+  uint32_t max_contrib[N_BLK];
+};
 
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+__device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSmem& sm) {
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
   const uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y;
-  const uint32_t px = tile_x * TILE_X + (tid & (TILE_X - 1));
-  const uint32_t py = tile_y * TILE_Y + (tid >> 4);
+  const uint32_t px = tile_x * TILE_X + pix_x_in_tile(warp, lane);
+  const uint32_t py = tile_y * TILE_Y + pix_y_in_tile(warp, lane);
   const bool inside = px < (uint32_t)a.W && py < (uint32_t)a.H;
   const uint32_t pix_id = (uint32_t)a.W * py + px;
   const float2 pixf = {(float)px, (float)py};
+  const float tile_px = (float)(tile_x * TILE_X), tile_py = (float)(tile_y * TILE_Y);
   const size_t HW = (size_t)a.H * a.W;
 
   const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
   if (range.y == range.x) return;
 
-  const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
-             normalize_depth = a.config[1] > 0;
-  const bool depth_diff = surface && per_pixel_depth;
-
   const float T_final = inside ? a.final_T[pix_id] : 0;
-  const float D_final = inside && normalize_depth ? a.final_D[pix_id] : 0;
+  const float D_final = inside && NORM_DEPTH ? a.final_D[pix_id] : 0;
   const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0;
 
   // deepest contributor of the tile: nothing behind it receives a gradient
@@ -104,26 +111,27 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs 
     uint32_t m = last_contributor;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) s_max_contrib[warp] = m;
+    if (lane == 0) sm.max_contrib[warp] = m;
   }
 #pragma unroll
-  for (int k = 0; k < GACC_FLOATS; ++k) s_acc[tid][k] = 0.f;
+  for (int k = 0; k < GACC_FLOATS; ++k) sm.acc[tid][k] = 0.f;
   __syncthreads();
   uint32_t tile_depth = 0;
 #pragma unroll
-  for (int w = 0; w < TILE_PIX / 32; ++w) tile_depth = max(tile_depth, s_max_contrib[w]);
+  for (int w = 0; w < N_BLK; ++w) tile_depth = max(tile_depth, sm.max_contrib[w]);
   if (tile_depth == 0) return;
   // the tile's list, restricted to [range.x, range.x + tile_depth), walked from the back
   const uint32_t list_end = range.x + tile_depth;
-  int toDo = (int)tile_depth;
-  const int rounds = (toDo + BWD_BATCH - 1) / BWD_BATCH;
+  const int rounds = (tile_depth + BWD_BATCH - 1) / BWD_BATCH;
 
   float dL_dpixC[3] = {0.f, 0.f, 0.f}, dL_dpixN[3] = {0.f, 0.f, 0.f}, dL_dpixD = 0.f, dL_dpixO = 0.f;
   if (inside) {
 #pragma unroll
     for (int i = 0; i < 3; i++) dL_dpixC[i] = a.dL_dpixcolor[i * HW + pix_id];
+    if (SURFACE) {
 #pragma unroll
-    for (int i = 0; i < 3; i++) dL_dpixN[i] = a.dL_dpixnormal[i * HW + pix_id];
+      for (int i = 0; i < 3; i++) dL_dpixN[i] = a.dL_dpixnormal[i * HW + pix_id];
+    }
     dL_dpixD = a.dL_dpixdepth[pix_id] * 1;
     dL_dpixO = a.dL_dpixopac[pix_id];
   }
@@ -131,135 +139,170 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs 
 #pragma unroll
   for (int i = 0; i < 3; i++) bg_dot_dpixel += a.bg[i] * dL_dpixC[i];
 
+  // pixel constants of the depth terms (backward.cu:760-777): the channel gradient is divided
+  // by (1 - T_final) when depth is normalised, and the normalisation adds
+  // g_d * D_final / (1-T_f)^2 * (-T_f) / ((1-alpha) * T) to dL/dalpha.
+  float dL_ddepth_ch = dL_dpixD, norm_k = 0.f;
+  if (NORM_DEPTH) {
+    dL_ddepth_ch = dL_dpixD / (1.f - T_final);
+    norm_k = dL_dpixD * D_final / (1.f - T_final) / (1.f - T_final) * -T_final;
+  }
+  // background / opacity / un-normalised depth terms all scale with T_final / (1 - alpha)
+  float tf_k = dL_dpixO * T_final - T_final * bg_dot_dpixel;
+  if (!NORM_DEPTH) tf_k -= T_final * (10 * dL_dpixD);
+
   float T = T_final;
-  uint32_t contributor = tile_depth;
   float accum_rec[3] = {0.f, 0.f, 0.f}, accum_rec_n[3] = {0.f, 0.f, 0.f}, accum_rec_d = 0.f;
   float last_alpha = 0.f;
   float last_color[3] = {0.f, 0.f, 0.f}, last_normal[3] = {0.f, 0.f, 0.f}, last_depth = 0.f;
   const float ddelx_dx = 0.5 * a.W;
   const float ddely_dy = 0.5 * a.H;
 
-  for (int i = 0; i < rounds; i++, toDo -= BWD_BATCH) {
+  for (int i = 0; i < rounds; i++) {
+    // ---- stage (from the back), cull against the tile, compact in walk order ---------
     const uint32_t progress = i * BWD_BATCH + tid;
-    const bool have = progress < tile_depth;
-    if (have) {
-      const uint32_t id = a.point_list[list_end - progress - 1];
-      const float4* rec = reinterpret_cast<const float4*>(a.records + (size_t)id * REC_FLOATS);
-      s_id[tid] = id;
-      s_q0[tid] = __ldg(rec + 0);
-      s_q1[tid] = __ldg(rec + 1);
-      s_q2[tid] = __ldg(rec + 2);
-      s_q3[tid] = __ldg(rec + 3);
-      s_q4[tid] = __ldg(rec + 4);
+    uint32_t mask = 0, id = 0;
+    const float4* rec = nullptr;
+    float4 q0, q1;
+    if (progress < tile_depth) {
+      id = a.point_list[list_end - progress - 1];
+      rec = reinterpret_cast<const float4*>(a.records + (size_t)id * REC_FLOATS);
+      q0 = __ldg(rec + 0);
+      q1 = __ldg(rec + 1);
+      mask = tile_block_mask(q0, q1, tile_px, tile_py);
+    }
+    const uint32_t keep_ballot = __ballot_sync(0xffffffffu, mask != 0);
+    if (lane == 0) sm.wcount[warp] = __popc(keep_ballot);
+    __syncthreads();
+    uint32_t slot = __popc(keep_ballot & lanemask_lt()), n = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < N_BLK; ++w) {
+      const uint32_t c = sm.wcount[w];
+      if (w < warp) slot += c;
+      n += c;
+    }
+    if (mask != 0) {
+      sm.q0[slot] = q0;
+      sm.q1[slot] = q1;
+      sm.q2[slot] = __ldg(rec + 2);
+      if (SURFACE) sm.q3[slot] = __ldg(rec + 3);
+      if (DEPTH_DIFF) sm.q4[slot] = __ldg(rec + 4);
+      sm.id[slot] = id;
+      sm.pos[slot] = tile_depth - 1 - progress;
+      sm.mask[slot] = (uint8_t)mask;
     }
     __syncthreads();
 
-    const int n = min(BWD_BATCH, toDo);
-    for (int j = 0; j < n; j++) {
-      contributor--;
-      bool live = contributor < last_contributor;
-      // warp-uniform early out before touching shared memory
-      if (!__any_sync(0xffffffffu, live)) continue;
+    for (uint32_t c0 = 0; c0 < n; c0 += 32) {
+      const uint32_t jj = c0 + lane;
+      const bool mine = jj < n && ((sm.mask[jj] >> warp) & 1u);
+      uint32_t bits = __ballot_sync(0xffffffffu, mine);
+      while (bits) {
+        const uint32_t j = c0 + __ffs(bits) - 1;
+        bits &= bits - 1;
+        bool live = sm.pos[j] < last_contributor;
+        const float4 q0j = sm.q0[j];
+        const float4 q1j = sm.q1[j];
+        const float2 d = {q0j.x - pixf.x, q0j.y - pixf.y};
+        const float dist = (q0j.z * d.x * d.x + q1j.x * d.y * d.y) + 2 * q0j.w * d.x * d.y;
+        const float power = -0.5f * dist;
+        live = live && !(power > 0.0f) && !(power < q1j.z);
+        if (!__any_sync(0xffffffffu, live)) continue;
+        const float G = exp(power);
+        const float alpha = min(0.99f, q1j.y * G);
+        live = live && !(alpha < 1.0f / 255.0f);
+        if (!__any_sync(0xffffffffu, live)) continue;
 
-      const float4 q0 = s_q0[j];
-      const float4 q1 = s_q1[j];
-      const float2 d = {q0.x - pixf.x, q0.y - pixf.y};
-      const float dist = (q0.z * d.x * d.x + q1.x * d.y * d.y) + 2 * q0.w * d.x * d.y;
-      const float power = -0.5f * dist;
-      live = live && !(power > 0.0f);
-      const float G = exp(power);
-      float alpha = min(0.99f, q1.y * G);
-      live = live && !(alpha < 1.0f / 255.0f);
-      if (!__any_sync(0xffffffffu, live)) continue;
-
-      float v[16];
+        float v[16];
 #pragma unroll
-      for (int k = 0; k < 16; ++k) v[k] = 0.f;
+        for (int k = 0; k < 16; ++k) v[k] = 0.f;
 
-      if (live) {
-        T = T / (1.f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        const float4 q2 = s_q2[j];
-        const float4 q4 = depth_diff ? s_q4[j] : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float J6 = depth_diff ? q1.w : 0.f, J9 = depth_diff ? q2.w : 0.f;
+        if (live) {
+          const float T_behind = T;  // transmittance after this Gaussian (front-to-back)
+          const float rcp = __frcp_rn(1.f - alpha);
+          T = T * rcp;
+          const float dchannel_dcolor = alpha * T;
+          const float4 q2 = sm.q2[j];
 
-        float dL_dalpha = 0.0f;
-        const float col[3] = {q2.x, q2.y, q2.z};
-#pragma unroll
-        for (int ch = 0; ch < 3; ch++) {
-          const float c_cur = col[ch];
-          accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-          last_color[ch] = c_cur;
-          const float dL_dchannel = dL_dpixC[ch];
-          dL_dalpha += (c_cur - accum_rec[ch]) * dL_dchannel;
-          v[GA_DC0 + ch] = dchannel_dcolor * dL_dchannel;
-        }
-        if (surface) {
-          const float4 q3 = s_q3[j];
-          const float nrm[3] = {q3.x, q3.y, q3.z};
+          float dL_dalpha = 0.0f;
+          const float col[3] = {q2.x, q2.y, q2.z};
 #pragma unroll
           for (int ch = 0; ch < 3; ch++) {
-            const float n_cur = nrm[ch];
-            accum_rec_n[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_rec_n[ch];
-            last_normal[ch] = n_cur;
-            const float dL_dchannel = dL_dpixN[ch];
-            dL_dalpha += (n_cur - accum_rec_n[ch]) * dL_dchannel;
-            v[GA_DN0 + ch] = dchannel_dcolor * dL_dchannel * 10;
+            const float c_cur = col[ch];
+            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+            last_color[ch] = c_cur;
+            const float dL_dchannel = dL_dpixC[ch];
+            dL_dalpha += (c_cur - accum_rec[ch]) * dL_dchannel;
+            v[GA_DC0 + ch] = dchannel_dcolor * dL_dchannel;
           }
-        }
-        {
-          float d_cur = q1.z;
-          if (depth_diff) {
-            const float dif_u0 = d.x * q4.x + d.y * q4.y;
-            const float dif_u1 = d.x * q4.z + d.y * q4.w;
-            d_cur -= dif_u0 * J6 + dif_u1 * J9;
+          float J6 = 0.f, J9 = 0.f;
+          float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (SURFACE) {
+            const float4 q3 = sm.q3[j];
+            const float nrm[3] = {q3.x, q3.y, q3.z};
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) {
+              const float n_cur = nrm[ch];
+              accum_rec_n[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_rec_n[ch];
+              last_normal[ch] = n_cur;
+              const float dL_dchannel = dL_dpixN[ch];
+              dL_dalpha += (n_cur - accum_rec_n[ch]) * dL_dchannel;
+              v[GA_DN0 + ch] = dchannel_dcolor * dL_dchannel * 10;
+            }
+            if (DEPTH_DIFF) {
+              J6 = q2.w;
+              J9 = q3.w;
+              q4 = sm.q4[j];
+            }
           }
-          accum_rec_d = last_alpha * last_depth + (1.f - last_alpha) * accum_rec_d;
-          last_depth = d_cur;
-          float dL_dchannel = dL_dpixD, dL_dalpha_depth = 0;
-          if (normalize_depth) {
-            dL_dchannel /= (1.f - T_final);
-            dL_dalpha_depth +=
-                dL_dpixD * D_final / (1.f - T_final) / (1.f - T_final) * -T_final / (1 - alpha) / T;
+          {
+            float d_cur = q1j.w;
+            if (DEPTH_DIFF) {
+              const float dif_u0 = d.x * q4.x + d.y * q4.y;
+              const float dif_u1 = d.x * q4.z + d.y * q4.w;
+              d_cur -= dif_u0 * J6 + dif_u1 * J9;
+            }
+            accum_rec_d = last_alpha * last_depth + (1.f - last_alpha) * accum_rec_d;
+            last_depth = d_cur;
+            float dL_dalpha_depth = 0;
+            if (NORM_DEPTH) dL_dalpha_depth += norm_k / T_behind;  // = norm_k / ((1-alpha) * T)
+            dL_dalpha_depth += (d_cur - accum_rec_d) * dL_ddepth_ch;
+            v[GA_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
+            dL_dalpha += dL_dalpha_depth;
           }
-          dL_dalpha_depth += (d_cur - accum_rec_d) * dL_dchannel;
-          v[GA_DD] = dchannel_dcolor * dL_dchannel * 1;
-          dL_dalpha += dL_dalpha_depth;
-        }
-        dL_dalpha *= T;
-        dL_dalpha += dL_dpixO * T_final / (1 - alpha);
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
-        if (!normalize_depth) dL_dalpha += (-T_final / (1.f - alpha)) * (10 * dL_dpixD);
+          dL_dalpha *= T;
+          dL_dalpha += tf_k * rcp;
+          last_alpha = alpha;
 
-        const float dL_ddist = dL_dalpha * q1.y * -0.5f * G;
-        float ndc_x = dL_ddist * 2 * (q0.z * d.x + q0.w * d.y) * ddelx_dx;
-        float ndc_y = dL_ddist * 2 * (q1.x * d.y + q0.w * d.x) * ddely_dy;
-        if (depth_diff) {
-          ndc_x += 1 * -dL_dpixD * (J6 * q4.x + J9 * q4.z);
-          ndc_y += 1 * -dL_dpixD * (J6 * q4.y + J9 * q4.w);
+          const float dL_ddist = dL_dalpha * q1j.y * -0.5f * G;
+          float ndc_x = dL_ddist * 2 * (q0j.z * d.x + q0j.w * d.y) * ddelx_dx;
+          float ndc_y = dL_ddist * 2 * (q1j.x * d.y + q0j.w * d.x) * ddely_dy;
+          if (DEPTH_DIFF) {
+            ndc_x += 1 * -dL_dpixD * (J6 * q4.x + J9 * q4.z);
+            ndc_y += 1 * -dL_dpixD * (J6 * q4.y + J9 * q4.w);
+          }
+          v[GA_DMX] = ndc_x;
+          v[GA_DMY] = ndc_y;
+          v[GA_DCA] = dL_ddist * (d.x * d.x);
+          v[GA_DCB] = dL_ddist * (1 * d.x * d.y);
+          v[GA_DCC] = dL_ddist * (d.y * d.y);
+          v[GA_DO] = G * dL_dalpha;
         }
-        v[GA_DMX] = ndc_x;
-        v[GA_DMY] = ndc_y;
-        v[GA_DCA] = dL_ddist * (d.x * d.x);
-        v[GA_DCB] = dL_ddist * (1 * d.x * d.y);
-        v[GA_DCC] = dL_ddist * (d.y * d.y);
-        v[GA_DO] = G * dL_dalpha;
+
+        const float total = warp_reduce16(v, lane);
+        if ((lane & 1) == 0 && (lane >> 1) < 13) atomicAdd(&sm.acc[j][lane >> 1], total);
       }
-
-      const float total = warp_reduce16(v, lane);
-      if ((lane & 1) == 0 && (lane >> 1) < 13) atomicAdd(&s_acc[j][lane >> 1], total);
     }
     __syncthreads();
 
-    // flush this batch: thread t owns the Gaussian it staged
-    if (have) {
-      float* acc = s_acc[tid];
+    // flush this batch: thread t owns compacted entry t
+    if ((uint32_t)tid < n) {
+      float* acc = sm.acc[tid];
       bool any = false;
 #pragma unroll
       for (int k = 0; k < 13; ++k) any = any || (acc[k] != 0.f);
       if (any) {
-        float* g = a.gacc + (size_t)s_id[tid] * GACC_FLOATS;
+        float* g = a.gacc + (size_t)sm.id[tid] * GACC_FLOATS;
         red_add_v4(g + 0, acc[0], acc[1], acc[2], acc[3]);
         red_add_v4(g + 4, acc[4], acc[5], acc[6], acc[7]);
         red_add_v4(g + 8, acc[8], acc[9], acc[10], acc[11]);
@@ -268,8 +311,26 @@ __global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs 
         for (int k = 0; k < 13; ++k) acc[k] = 0.f;
       }
     }
-    // next iteration's staging writes s_q*/s_id only after this barrier
-    __syncthreads();
+    // the next round's staging writes happen after its first barrier; the flush above only
+    // touches rows < n of this round, which the next round's atomics reach after that barrier
+  }
+}
+
+// The config flags live in device memory (backward.cu:581): one kernel, specialised bodies
+// selected by a uniform branch.
+__global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs a) {
+  __shared__ BlendBwdSmem sm;
+  const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
+             normalize_depth = a.config[1] > 0;
+  if (surface && per_pixel_depth) {
+    if (normalize_depth) blend_bwd_body<true, true, true>(a, sm);
+    else blend_bwd_body<true, true, false>(a, sm);
+  } else if (surface) {
+    if (normalize_depth) blend_bwd_body<true, false, true>(a, sm);
+    else blend_bwd_body<true, false, false>(a, sm);
+  } else {
+    if (normalize_depth) blend_bwd_body<false, false, true>(a, sm);
+    else blend_bwd_body<false, false, false>(a, sm);
   }
 }
 

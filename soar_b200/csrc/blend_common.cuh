@@ -1,0 +1,75 @@
+// Shared pieces of the tile blend kernels (forward and backward):
+//   * the pixel <-> thread mapping: a 16x16 tile is eight 8x4 pixel blocks, one per warp
+//     (an 8x4 block is touched by fewer Gaussians than a 16x2 row pair, so more warp
+//     iterations can be skipped);
+//   * a conservative "can this Gaussian reach alpha >= 1/255 anywhere in this pixel
+//     rectangle" test, used to drop (Gaussian, tile) pairs at staging time and to give every
+//     warp the list of Gaussians that can touch ITS 8x4 block. A pair that is dropped would
+//     have failed the reference's `alpha < 1/255` test (forward.cu:545 / backward.cu:663) at
+//     every pixel of the rectangle, so skipping it changes neither images, n_contrib nor
+//     gradients; pairs that survive still take the reference's exact per-pixel tests.
+#pragma once
+#include "common.cuh"
+#include "layout.h"
+
+namespace soar {
+
+constexpr int BLK_W = 8, BLK_H = 4;  // pixel block of one warp
+constexpr int N_BLK = TILE_PIX / 32;  // 8 blocks per tile: 2 across, 4 down
+
+__device__ __forceinline__ uint32_t pix_x_in_tile(uint32_t warp, uint32_t lane) {
+  return (warp & 1u) * BLK_W + (lane & 7u);
+}
+__device__ __forceinline__ uint32_t pix_y_in_tile(uint32_t warp, uint32_t lane) {
+  return (warp >> 1) * BLK_H + (lane >> 3);
+}
+
+// q(d) = A dx^2 + 2 B dx dy + C dy^2 minimised over the box dx in [dx0,dx1], dy in [dy0,dy1]
+// (d = Gaussian centre - pixel). power = -q/2. Returns true when some pixel of the box MAY
+// pass `power >= thr_exact`; thr (REC_THR) already sits 0.02 below the exact threshold and a
+// further 1e-5 * (magnitude of the terms) absorbs the rounding of both this evaluation and
+// the kernels' own power polynomial. Non positive-definite conics and NaNs are never culled.
+__device__ __forceinline__ bool box_may_contribute(float A, float B, float C, float thr, float dx0,
+                                                   float dx1, float dy0, float dy1) {
+  const float det = A * C - B * B;
+  if (!(A > 0.f && C > 0.f && det > 0.f)) return true;
+  if (dx0 <= 0.f && dx1 >= 0.f && dy0 <= 0.f && dy1 >= 0.f) return true;  // centre inside
+  const float nBoverC = -B / C, nBoverA = -B / A;
+  float qmin;
+  {
+    const float y0 = fminf(fmaxf(nBoverC * dx0, dy0), dy1);
+    const float y1 = fminf(fmaxf(nBoverC * dx1, dy0), dy1);
+    const float v0 = A * dx0 * dx0 + (2.f * B * dx0 + C * y0) * y0;
+    const float v1 = A * dx1 * dx1 + (2.f * B * dx1 + C * y1) * y1;
+    qmin = fminf(v0, v1);
+  }
+  {
+    const float x0 = fminf(fmaxf(nBoverA * dy0, dx0), dx1);
+    const float x1 = fminf(fmaxf(nBoverA * dy1, dx0), dx1);
+    const float v0 = C * dy0 * dy0 + (2.f * B * dy0 + A * x0) * x0;
+    const float v1 = C * dy1 * dy1 + (2.f * B * dy1 + A * x1) * x1;
+    qmin = fminf(qmin, fminf(v0, v1));
+  }
+  const float mx = fmaxf(fabsf(dx0), fabsf(dx1)), my = fmaxf(fabsf(dy0), fabsf(dy1));
+  const float mag = A * mx * mx + C * my * my + 2.f * fabsf(B) * mx * my;
+  return !(0.5f * qmin > -thr + 1e-5f * mag);
+}
+
+// 8-bit mask of the tile's 8x4 blocks a Gaussian may contribute to (bit = warp index).
+__device__ __forceinline__ uint32_t tile_block_mask(const float4 q0, const float4 q1, float tile_px,
+                                                    float tile_py) {
+  const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
+  const float gx = q0.x - tile_px, gy = q0.y - tile_py;  // centre relative to the tile origin
+  // whole tile first: pixels 0..15 in both axes
+  if (!box_may_contribute(A, B, C, thr, gx - 15.f, gx, gy - 15.f, gy)) return 0u;
+  uint32_t mask = 0;
+#pragma unroll
+  for (int b = 0; b < N_BLK; ++b) {
+    const float bx = (float)((b & 1) * BLK_W), by = (float)((b >> 1) * BLK_H);
+    if (box_may_contribute(A, B, C, thr, gx - bx - (BLK_W - 1), gx - bx, gy - by - (BLK_H - 1), gy - by))
+      mask |= 1u << b;
+  }
+  return mask;
+}
+
+}  // namespace soar

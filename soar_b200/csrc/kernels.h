@@ -26,20 +26,24 @@ struct PreprocessArgs {
   int* radii;
   float* records;
   uint32_t* tiles_touched;
+  uint32_t* depth_keys;  // depth bits of visible Gaussians, 0xffffffff for culled ones
   uint32_t* error_flag;
 };
 int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream);
 
-int launch_scan(const uint32_t* in, uint32_t* out, int n, void* status_region,
-                size_t status_bytes, cudaStream_t stream);
-int launch_duplicate_keys(int P, const float* records, const uint32_t* tiles_touched,
-                          const uint32_t* offsets, unsigned long long* keys, uint32_t* values,
-                          uint32_t grid_x, cudaStream_t stream);
-int launch_radix_sort(unsigned long long* keys[2], uint32_t* values[2], uint32_t n, int end_bit,
-                      bool descending, uint32_t* ghist, uint32_t* status, int n_sort_tiles,
-                      int* result_buf, cudaStream_t stream);
-int launch_tile_ranges(uint32_t L, const unsigned long long* keys, uint2* ranges, int n_tiles,
+int launch_scan(const uint32_t* in, const uint32_t* index, uint32_t* out, int n,
+                void* status_region, cudaStream_t stream);
+int launch_duplicate_tiles(int P, const float* records, const uint32_t* perm,
+                           const uint32_t* offsets_incl, uint32_t* keys, uint32_t* values,
+                           uint32_t grid_x, bool descending, int tile_bits, uint32_t* ghist,
+                           cudaStream_t stream);
+int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int end_bit,
+                      bool descending, bool iota_values, bool have_hist, uint32_t* ghist,
+                      uint32_t* status, int n_sort_tiles, int* result_buf, cudaStream_t stream);
+int launch_tile_ranges(uint32_t L, const uint32_t* keys, uint2* ranges, int n_tiles,
                        cudaStream_t stream);
+int launch_debug_keys(uint32_t L, const uint32_t* tiles, const uint32_t* ids, const float* records,
+                      unsigned long long* out, cudaStream_t stream);
 
 struct BlendFwdArgs {
   int W, H, grid_x;

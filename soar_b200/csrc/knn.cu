@@ -111,7 +111,7 @@ __device__ __forceinline__ uint32_t spread10(uint32_t x) {
 
 __global__ void __launch_bounds__(256)
 knn_morton_kernel(int P, const float* __restrict__ pts, const uint32_t* __restrict__ bbox,
-                  unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+                  uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
   uint32_t code = 0;
@@ -276,8 +276,8 @@ int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* work
   Aabb* box[3] = {reinterpret_cast<Aabb*>(ws + L.boxes[0]), reinterpret_cast<Aabb*>(ws + L.boxes[1]),
                   reinterpret_cast<Aabb*>(ws + L.boxes[2])};
   char* sw = ws + L.sort;
-  unsigned long long* keys[2] = {reinterpret_cast<unsigned long long*>(sw + L.BL.keys[0]),
-                                 reinterpret_cast<unsigned long long*>(sw + L.BL.keys[1])};
+  uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(sw + L.BL.keys[0]),
+                       reinterpret_cast<uint32_t*>(sw + L.BL.keys[1])};
   uint32_t* vals[2] = {reinterpret_cast<uint32_t*>(sw + L.BL.values[0]),
                        reinterpret_cast<uint32_t*>(sw + L.BL.values[1])};
 
@@ -297,8 +297,8 @@ int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* work
   SOAR_LAUNCH_CHECK("knn_morton_kernel");
   SOAR_CUDA_TRY(cudaMemsetAsync(sw + L.BL.zero_begin, 0, L.BL.zero_bytes, stream));
   int res = 0;
-  int rc = launch_radix_sort(keys, vals, (uint32_t)P, 30, false,
-                             reinterpret_cast<uint32_t*>(sw + L.BL.ghist),
+  int rc = launch_radix_sort(keys, vals, (uint32_t)P, 30, false, /*iota_values=*/false,
+                             /*have_hist=*/false, reinterpret_cast<uint32_t*>(sw + L.BL.ghist),
                              reinterpret_cast<uint32_t*>(sw + L.BL.status), L.BL.n_sort_tiles, &res,
                              stream);
   if (rc) return rc;

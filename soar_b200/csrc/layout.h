@@ -15,14 +15,16 @@
 namespace soar {
 
 // ---- per-Gaussian record (24 floats = 96 B = 3 sectors) ------------------------
+// float4 #0 and #1 are all a pixel needs to decide whether a Gaussian contributes
+// (REC_THR: conservative lower bound on `power` below which alpha < 1/255 for sure).
 constexpr int REC_FLOATS = 24;
 enum RecSlot {
   REC_X = 0, REC_Y = 1, REC_CON_A = 2, REC_CON_B = 3,      // float4 #0
-  REC_CON_C = 4, REC_OPAC = 5, REC_DEPTH = 6, REC_J6 = 7,  // float4 #1
-  REC_R = 8, REC_G = 9, REC_B = 10, REC_J9 = 11,           // float4 #2
-  REC_NX = 12, REC_NY = 13, REC_NZ = 14, REC_VIEWCOS = 15, // float4 #3
+  REC_CON_C = 4, REC_OPAC = 5, REC_THR = 6, REC_DEPTH = 7, // float4 #1
+  REC_R = 8, REC_G = 9, REC_B = 10, REC_J6 = 11,           // float4 #2
+  REC_NX = 12, REC_NY = 13, REC_NZ = 14, REC_J9 = 15,      // float4 #3
   REC_J0 = 16, REC_J1 = 17, REC_J2 = 18, REC_J3 = 19,      // float4 #4
-  REC_RECT_X = 20, REC_RECT_Y = 21, REC_RADIUS = 22, REC_PAD = 23  // float4 #5 (bit-cast ints)
+  REC_RECT_X = 20, REC_RECT_Y = 21, REC_RADIUS = 22, REC_VIEWCOS = 23  // float4 #5 (ints bit-cast)
 };
 
 // ---- decoupled look-back scan of tiles_touched ----------------------------------
@@ -30,13 +32,29 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
+// ---- onesweep radix sort ------------------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 12;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 4;    // 32-bit keys
+constexpr int SORT_MAX_PASSES_R = 4;  // tile-id sort (up to 32 tile bits)
+inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
+
 struct GeomLayout {
   size_t records;        // float[P*24]
   size_t tiles_touched;  // u32[P]
-  size_t point_offsets;  // u32[P] inclusive prefix sum
-  size_t scan_status;    // u64[n_scan_tiles] + u32 ticket + u32 error flag (zeroed per call)
+  size_t point_offsets;  // u32[P] inclusive prefix sum of tiles_touched IN DEPTH ORDER
+  size_t depth_keys[2];  // u32[P] x2: depth bits (0xffffffff for culled), ping-pong
+  size_t perm[2];        // u32[P] x2: Gaussian indices, ping-pong; perm[0] holds the depth order
+  size_t zero_begin, zero_bytes;  // region zeroed per call:
+  size_t scan_status;    //   u64[n_scan_tiles] + u32 ticket + u32 error flag
   size_t scan_status_bytes;
+  size_t ghist;          //   u32[4*256] digit histograms of the depth sort
+  size_t sort_status;    //   u32[4*n_sort_tiles*256] look-back words + 4 tickets
   size_t total;
+  int n_sort_tiles;
 };
 
 inline GeomLayout geom_layout(size_t P) {
@@ -45,10 +63,18 @@ inline GeomLayout geom_layout(size_t P) {
   L.records = off;        off = align_up(off + P * REC_FLOATS * sizeof(float), 256);
   L.tiles_touched = off;  off = align_up(off + P * sizeof(uint32_t), 256);
   L.point_offsets = off;  off = align_up(off + P * sizeof(uint32_t), 256);
+  for (int i = 0; i < 2; ++i) { L.depth_keys[i] = off; off = align_up(off + P * sizeof(uint32_t), 256); }
+  for (int i = 0; i < 2; ++i) { L.perm[i] = off; off = align_up(off + P * sizeof(uint32_t), 256); }
   size_t n_tiles = (P + SCAN_TILE - 1) / SCAN_TILE;
+  L.zero_begin = off;
   L.scan_status = off;
   L.scan_status_bytes = align_up(n_tiles * sizeof(uint64_t) + 16, 256);
   off += L.scan_status_bytes;
+  L.ghist = off;          off = align_up(off + SORT_MAX_PASSES * SORT_RADIX * 4, 256);
+  L.n_sort_tiles = (int)((P + SORT_TILE - 1) / SORT_TILE);
+  L.sort_status = off;
+  off = align_up(off + ((size_t)SORT_MAX_PASSES * L.n_sort_tiles * SORT_RADIX + SORT_MAX_PASSES) * 4, 256);
+  L.zero_bytes = off - L.zero_begin;
   L.total = off + 256;
   return L;
 }
@@ -75,18 +101,11 @@ inline ImageLayout image_layout(int W, int H) {
   return L;
 }
 
-// ---- onesweep radix sort ------------------------------------------------------------
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 12;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
-constexpr int SORT_RADIX_BITS = 8;
-constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
-constexpr int SORT_MAX_PASSES = 8;
-
+// ---- (tile id, Gaussian index) pairs ------------------------------------------------
 struct BinningLayout {
-  size_t keys[2];    // u64[R] x2 (ping-pong)
-  size_t values[2];  // u32[R] x2
-  size_t ghist;      // u32[SORT_MAX_PASSES*256] digit histograms -> exclusive offsets
+  size_t keys[2];    // u32[R] x2 tile ids (ping-pong)
+  size_t values[2];  // u32[R] x2 Gaussian indices
+  size_t ghist;      // u32[passes*256] digit histograms -> exclusive offsets
   size_t status;     // u32[passes*n_sort_tiles*256] look-back words + u32 ticket per pass
   size_t zero_begin, zero_bytes;  // region that must be zero before sorting (ghist+status)
   size_t total;
@@ -96,21 +115,19 @@ struct BinningLayout {
 inline BinningLayout binning_layout(size_t R, int passes) {
   BinningLayout L;
   size_t off = 0;
-  L.keys[0] = off;   off = align_up(off + R * 8, 256);
-  L.keys[1] = off;   off = align_up(off + R * 8, 256);
+  L.keys[0] = off;   off = align_up(off + R * 4, 256);
+  L.keys[1] = off;   off = align_up(off + R * 4, 256);
   L.values[0] = off; off = align_up(off + R * 4, 256);
   L.values[1] = off; off = align_up(off + R * 4, 256);
   L.n_sort_tiles = (int)((R + SORT_TILE - 1) / SORT_TILE);
   L.zero_begin = off;
-  L.ghist = off;     off = align_up(off + SORT_MAX_PASSES * SORT_RADIX * 4, 256);
+  L.ghist = off;     off = align_up(off + SORT_MAX_PASSES_R * SORT_RADIX * 4, 256);
   L.status = off;
-  off = align_up(off + ((size_t)passes * L.n_sort_tiles * SORT_RADIX + SORT_MAX_PASSES) * 4, 256);
+  off = align_up(off + ((size_t)passes * L.n_sort_tiles * SORT_RADIX + SORT_MAX_PASSES_R) * 4, 256);
   L.zero_bytes = off - L.zero_begin;
   L.total = off + 256;
   return L;
 }
-
-inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
 
 // ---- backward scratch: per-Gaussian accumulator written by the blend backward ----
 // 16 floats: dcolor[3] dnormal[3] ddepth dmean2D.xy dconic.(a,b,c) dopacity pad[3]

@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
 
   a.radii[idx] = 0;
   a.tiles_touched[idx] = 0;
+  a.depth_keys[idx] = 0xffffffffu;
 
   const float* __restrict__ view = a.viewmatrix;
   const float* __restrict__ proj = a.projmatrix;
@@ -116,16 +117,27 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
   const int radius_i = my_radius;
   a.radii[idx] = radius_i;
   a.tiles_touched[idx] = (rect_max.y - rect_min.y) * (rect_max.x - rect_min.x);
+  a.depth_keys[idx] = __float_as_uint(p_view.z);
+
+  // Cull threshold for the blend kernels: a pixel contributes only when
+  // min(0.99, o*exp(power)) >= 1/255, i.e. power >= log(1/(255 o)). REC_THR sits 0.02 below
+  // that (2 % in alpha, far above any rounding of expf or of the power polynomial), so
+  // "power < REC_THR" proves alpha < 1/255 without evaluating expf; anything else still takes
+  // the reference's exact test. o <= 0 (or NaN) never contributes: +inf rejects every pixel
+  // only when the exact test would too, so keep such Gaussians on the exact path with -inf.
+  const float opac = a.opacities[idx];
+  float thr = -INFINITY;
+  if (opac > 0.f && opac < INFINITY) thr = -logf(255.0f * opac) - 0.02f;
 
   float4* rec = reinterpret_cast<float4*>(a.records + (size_t)idx * REC_FLOATS);
   rec[0] = make_float4(point_image.x, point_image.y, conic.x, conic.y);
-  rec[1] = make_float4(conic.z, a.opacities[idx], p_view.z, homo[6]);
-  rec[2] = make_float4(rgb[0], rgb[1], rgb[2], homo[9]);
-  rec[3] = make_float4(n_view.x, n_view.y, n_view.z, view_cos);
+  rec[1] = make_float4(conic.z, opac, thr, p_view.z);
+  rec[2] = make_float4(rgb[0], rgb[1], rgb[2], homo[6]);
+  rec[3] = make_float4(n_view.x, n_view.y, n_view.z, homo[9]);
   rec[4] = make_float4(homo[0], homo[1], homo[2], homo[3]);
   rec[5] = make_float4(__uint_as_float(rect_min.x | (rect_max.x << 16)),
                        __uint_as_float(rect_min.y | (rect_max.y << 16)),
-                       __int_as_float(radius_i), 0.f);
+                       __int_as_float(radius_i), view_cos);
 }
 
 int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream) {

@@ -43,7 +43,11 @@ def _debug_tensors(s, out_radii):
         p = lib.soar_rast_debug_ptr(what, P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr())
         return refdgr._from_ptr(p, n, dtype, s["means3D"].device)
 
-    return dict(R=R, keys=grab(0, R, torch.int64), point_list=grab(1, R, torch.int32),
+    keys = torch.empty(R, dtype=torch.int64, device=s["means3D"].device)
+    _capi.check(lib.soar_rast_debug_sorted_keys(P, W, H, R, geom.data_ptr(), binning.data_ptr(),
+                                                keys.data_ptr() if R else None, None), "debug keys")
+    torch.cuda.synchronize()
+    return dict(R=R, keys=keys, point_list=grab(1, R, torch.int32),
                 ranges=grab(2, 2 * T, torch.int32).view(T, 2), n_contrib=grab(3, H * W, torch.int32),
                 radii=radii)
 
