@@ -90,23 +90,35 @@ scan_lookback_kernel(const uint32_t* __restrict__ in, const uint32_t* __restrict
   }
   const uint32_t thread_excl = warp_off + incl - tsum;
 
-  if (tid == 0) {
+  // warp 0 resolves the tile's exclusive prefix: 32 predecessor status words per step
+  if (warp == 0) {
     uint32_t prefix = 0;
     if (tile == 0) {
-      st_relaxed_u64(&status[0], SCAN_FLAG_INCL | block_total);
+      if (lane == 0) st_relaxed_u64(&status[0], SCAN_FLAG_INCL | block_total);
     } else {
-      st_relaxed_u64(&status[tile], SCAN_FLAG_AGG | block_total);
+      if (lane == 0) st_relaxed_u64(&status[tile], SCAN_FLAG_AGG | block_total);
       int t = (int)tile - 1;
       while (true) {
-        unsigned long long s;
-        do { s = ld_relaxed_u64(&status[t]); } while ((s & SCAN_FLAG_MASK) == 0);
-        prefix += (uint32_t)s;
-        if ((s & SCAN_FLAG_MASK) == SCAN_FLAG_INCL) break;
-        --t;
+        const int tt = t - lane;
+        const unsigned long long s = tt >= 0 ? ld_relaxed_u64(&status[tt]) : SCAN_FLAG_INCL;
+        const unsigned long long flag = s & SCAN_FLAG_MASK;
+        const uint32_t not_ready = __ballot_sync(0xffffffffu, flag == 0);
+        const uint32_t incl = __ballot_sync(0xffffffffu, flag == SCAN_FLAG_INCL);
+        const uint32_t first_nr = not_ready ? (uint32_t)__ffs(not_ready) - 1u : 32u;
+        const uint32_t first_incl = incl ? (uint32_t)__ffs(incl) - 1u : 32u;
+        const bool finish = first_incl < first_nr;
+        const uint32_t take = finish ? first_incl + 1u : first_nr;  // lanes [0, take)
+        uint32_t val = (uint32_t)lane < take ? (uint32_t)s : 0u;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+        prefix += val;
+        if (finish) break;
+        t -= (int)take;
       }
-      st_relaxed_u64(&status[tile], SCAN_FLAG_INCL | (unsigned long long)(prefix + block_total));
+      if (lane == 0)
+        st_relaxed_u64(&status[tile], SCAN_FLAG_INCL | (unsigned long long)(prefix + block_total));
     }
-    s_prefix = prefix;
+    if (lane == 0) s_prefix = prefix;
   }
   __syncthreads();
   const uint32_t add = s_prefix + thread_excl;
@@ -244,6 +256,7 @@ constexpr uint32_t RS_FLAG_AGG = 1u << 30;
 constexpr uint32_t RS_FLAG_INCL = 2u << 30;
 constexpr uint32_t RS_FLAG_MASK = 3u << 30;
 constexpr uint32_t RS_VALUE_MASK = (1u << 30) - 1u;
+constexpr int RS_LB = 8;  // look-back words in flight per step
 
 // One pass over the keys builds the digit histograms of every pass.
 __global__ void __launch_bounds__(256)
@@ -364,17 +377,29 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
     const uint32_t digit_excl = off + incl - total;
     s_digit_excl[d] = digit_excl;
 
-    // decoupled look-back over predecessor tiles for this digit
+    // decoupled look-back over predecessor tiles for this digit; RS_LB status words are
+    // fetched per step so the chain costs one L2 round trip per RS_LB tiles, not per tile
     uint32_t prev = 0;
     if (tile != 0) {
       int t = (int)tile - 1;
-      while (true) {
-        uint32_t s;
-        const uint32_t* ps = status + (size_t)t * SORT_RADIX + d;
-        do { s = ld_relaxed_u32(ps); } while ((s & RS_FLAG_MASK) == 0);
-        prev += s & RS_VALUE_MASK;
-        if ((s & RS_FLAG_MASK) == RS_FLAG_INCL) break;
-        --t;
+      bool found = false;
+      while (!found) {
+        uint32_t s[RS_LB];
+#pragma unroll
+        for (int k = 0; k < RS_LB; ++k) {
+          const int tt = t - k;
+          s[k] = tt >= 0 ? ld_relaxed_u32(status + (size_t)tt * SORT_RADIX + d) : RS_FLAG_INCL;
+        }
+        int used = 0;
+#pragma unroll
+        for (int k = 0; k < RS_LB; ++k) {
+          if (!found && used == k && (s[k] & RS_FLAG_MASK) != 0) {
+            prev += s[k] & RS_VALUE_MASK;
+            used = k + 1;
+            found = (s[k] & RS_FLAG_MASK) == RS_FLAG_INCL;
+          }
+        }
+        t -= used;
       }
       st_relaxed_u32(my_status, RS_FLAG_INCL | ((prev + total) & RS_VALUE_MASK));
     }

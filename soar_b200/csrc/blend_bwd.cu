@@ -152,9 +152,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   if (!NORM_DEPTH) tf_k -= T_final * (10 * dL_dpixD);
 
   float T = T_final;
-  float accum_rec[3] = {0.f, 0.f, 0.f}, accum_rec_n[3] = {0.f, 0.f, 0.f}, accum_rec_d = 0.f;
-  float last_alpha = 0.f;
-  float last_color[3] = {0.f, 0.f, 0.f}, last_normal[3] = {0.f, 0.f, 0.f}, last_depth = 0.f;
+  float S = 0.f, cg_last = 0.f, last_alpha = 0.f;
   const float ddelx_dx = 0.5 * a.W;
   const float ddely_dy = 0.5 * a.H;
 
@@ -224,52 +222,41 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           const float dchannel_dcolor = alpha * T;
           const float4 q2 = sm.q2[j];
 
-          float dL_dalpha = 0.0f;
-          const float col[3] = {q2.x, q2.y, q2.z};
-#pragma unroll
-          for (int ch = 0; ch < 3; ch++) {
-            const float c_cur = col[ch];
-            accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-            last_color[ch] = c_cur;
-            const float dL_dchannel = dL_dpixC[ch];
-            dL_dalpha += (c_cur - accum_rec[ch]) * dL_dchannel;
-            v[GA_DC0 + ch] = dchannel_dcolor * dL_dchannel;
-          }
+          // dL/dalpha needs sum_ch g_ch * (c_ch - accum_rec_ch) with
+          // accum_rec_ch <- last_alpha * last_c_ch + (1 - last_alpha) * accum_rec_ch for the 3
+          // colour, 3 normal and 1 depth channels (backward.cu:700-770). The recurrence is
+          // linear, so S = sum_ch g_ch * accum_rec_ch is carried as ONE scalar:
+          // S <- last_alpha * cg_last + (1 - last_alpha) * S, cg = sum_ch g_ch * c_ch.
+          float cg = q2.x * dL_dpixC[0] + q2.y * dL_dpixC[1] + q2.z * dL_dpixC[2];
+          v[GA_DC0 + 0] = dchannel_dcolor * dL_dpixC[0];
+          v[GA_DC0 + 1] = dchannel_dcolor * dL_dpixC[1];
+          v[GA_DC0 + 2] = dchannel_dcolor * dL_dpixC[2];
           float J6 = 0.f, J9 = 0.f;
           float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
           if (SURFACE) {
             const float4 q3 = sm.q3[j];
-            const float nrm[3] = {q3.x, q3.y, q3.z};
-#pragma unroll
-            for (int ch = 0; ch < 3; ch++) {
-              const float n_cur = nrm[ch];
-              accum_rec_n[ch] = last_alpha * last_normal[ch] + (1.f - last_alpha) * accum_rec_n[ch];
-              last_normal[ch] = n_cur;
-              const float dL_dchannel = dL_dpixN[ch];
-              dL_dalpha += (n_cur - accum_rec_n[ch]) * dL_dchannel;
-              v[GA_DN0 + ch] = dchannel_dcolor * dL_dchannel * 10;
-            }
+            cg += q3.x * dL_dpixN[0] + q3.y * dL_dpixN[1] + q3.z * dL_dpixN[2];
+            v[GA_DN0 + 0] = dchannel_dcolor * dL_dpixN[0] * 10;
+            v[GA_DN0 + 1] = dchannel_dcolor * dL_dpixN[1] * 10;
+            v[GA_DN0 + 2] = dchannel_dcolor * dL_dpixN[2] * 10;
             if (DEPTH_DIFF) {
               J6 = q2.w;
               J9 = q3.w;
               q4 = sm.q4[j];
             }
           }
-          {
-            float d_cur = q1j.w;
-            if (DEPTH_DIFF) {
-              const float dif_u0 = d.x * q4.x + d.y * q4.y;
-              const float dif_u1 = d.x * q4.z + d.y * q4.w;
-              d_cur -= dif_u0 * J6 + dif_u1 * J9;
-            }
-            accum_rec_d = last_alpha * last_depth + (1.f - last_alpha) * accum_rec_d;
-            last_depth = d_cur;
-            float dL_dalpha_depth = 0;
-            if (NORM_DEPTH) dL_dalpha_depth += norm_k / T_behind;  // = norm_k / ((1-alpha) * T)
-            dL_dalpha_depth += (d_cur - accum_rec_d) * dL_ddepth_ch;
-            v[GA_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
-            dL_dalpha += dL_dalpha_depth;
+          float d_cur = q1j.w;
+          if (DEPTH_DIFF) {
+            const float dif_u0 = d.x * q4.x + d.y * q4.y;
+            const float dif_u1 = d.x * q4.z + d.y * q4.w;
+            d_cur -= dif_u0 * J6 + dif_u1 * J9;
           }
+          cg += d_cur * dL_ddepth_ch;
+          v[GA_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
+          S = last_alpha * cg_last + (1.f - last_alpha) * S;
+          cg_last = cg;
+          float dL_dalpha = cg - S;
+          if (NORM_DEPTH) dL_dalpha += norm_k / T_behind;  // = norm_k / ((1-alpha) * T)
           dL_dalpha *= T;
           dL_dalpha += tf_k * rcp;
           last_alpha = alpha;
@@ -318,7 +305,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
 
 // The config flags live in device memory (backward.cu:581): one kernel, specialised bodies
 // selected by a uniform branch.
-__global__ void __launch_bounds__(TILE_PIX) blend_bwd_kernel(const BlendBwdArgs a) {
+__global__ void __launch_bounds__(TILE_PIX, 3) blend_bwd_kernel(const BlendBwdArgs a) {
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;

@@ -25,7 +25,9 @@ __device__ __forceinline__ void warp_atomic_add(float* dst, float v) {
   if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(dst, v);
 }
 
-template <bool LRN_CAM>
+// SHV: SH coefficients per Gaussian moved with 16-byte loads/stores (16 or 4; rows are then
+// 192 / 48 bytes, 16-byte aligned); 0 = generic scalar path for any M.
+template <bool LRN_CAM, int SHV>
 __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
   // config lives on the device: both variants are launched, the one that does
   // not match config[3] (lrn_cam) retires immediately.
@@ -56,8 +58,14 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
     p = a.g.dL_dscales + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f;
     reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (a.M > 0 && a.g.dL_dsh) {
-      p = a.g.dL_dsh + (size_t)idx * a.M * 3;
-      for (int i = 0; i < a.M * 3; ++i) p[i] = 0.f;
+      if (SHV > 0) {
+        float4* p4 = reinterpret_cast<float4*>(a.g.dL_dsh + (size_t)idx * SHV * 3);
+#pragma unroll
+        for (int i = 0; i < SHV * 3 / 4; ++i) p4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        p = a.g.dL_dsh + (size_t)idx * a.M * 3;
+        for (int i = 0; i < a.M * 3; ++i) p[i] = 0.f;
+      }
     }
   }
 
@@ -235,12 +243,23 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
 
     // ---- SH backward (backward.cu:20-158) ----------------------------------------------
     if (a.shs != nullptr) {
-      const float* __restrict__ sh = a.shs + (size_t)idx * a.M * 3;
+      float sh_local[SHV > 0 ? SHV * 3 : 4];
+      if (SHV > 0) {
+        const float4* s4 = reinterpret_cast<const float4*>(a.shs + (size_t)idx * SHV * 3);
+#pragma unroll
+        for (int i = 0; i < SHV * 3 / 4; ++i) {
+          const float4 t = __ldg(s4 + i);
+          sh_local[4 * i + 0] = t.x; sh_local[4 * i + 1] = t.y;
+          sh_local[4 * i + 2] = t.z; sh_local[4 * i + 3] = t.w;
+        }
+      }
+      const float* __restrict__ sh = SHV > 0 ? sh_local : a.shs + (size_t)idx * a.M * 3;
       float* dsh = a.g.dL_dsh + (size_t)idx * a.M * 3;
+      const int Deg = SHV == 4 ? min(a.D, 1) : a.D;  // SHV == 4 holds degree <= 1 only
       const float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
       const float3 dir_orig = {mean.x - cam.x, mean.y - cam.y, mean.z - cam.z};
       float rgb[3];
-      const unsigned clamp_mask = sh_to_rgb(a.D, sh, mean, cam, rgb);
+      const unsigned clamp_mask = sh_to_rgb(Deg, sh, mean, cam, rgb);
       const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
       const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
       float dRGB[3];
@@ -252,7 +271,7 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
       for (int i = 0; i < 16; ++i) basis[i] = 0.f;
       float dx[3] = {0, 0, 0}, dy[3] = {0, 0, 0}, dz[3] = {0, 0, 0};
       basis[0] = kSH_C0;
-      if (a.D > 0) {
+      if (Deg > 0) {
         basis[1] = -kSH_C1 * y;
         basis[2] = kSH_C1 * z;
         basis[3] = -kSH_C1 * x;
@@ -262,7 +281,7 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
           dy[c] = -kSH_C1 * sh[1 * 3 + c];
           dz[c] = kSH_C1 * sh[2 * 3 + c];
         }
-        if (a.D > 1) {
+        if (Deg > 1) {
           const float xx = x * x, yy = y * y, zz = z * z;
           const float xy = x * y, yz = y * z, xz = x * z;
           basis[4] = kSH_C2[0] * xy;
@@ -280,7 +299,7 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
                      kSH_C2[4] * 2.f * -y * s8;
             dz[c] += kSH_C2[1] * y * s5 + kSH_C2[2] * 2.f * 2.f * z * s6 + kSH_C2[3] * x * s7;
           }
-          if (a.D > 2) {
+          if (Deg > 2) {
             basis[9] = kSH_C3[0] * y * (3.f * xx - yy);
             basis[10] = kSH_C3[1] * xy * z;
             basis[11] = kSH_C3[2] * y * (4.f * zz - xx - yy);
@@ -308,12 +327,27 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
           }
         }
       }
-      const int active = (a.D + 1) * (a.D + 1);
-      for (int i = 0; i < a.M; ++i) {
-        const float b = (i < active && i < 16) ? basis[i] : 0.f;
-        dsh[3 * i + 0] = b * dRGB[0];
-        dsh[3 * i + 1] = b * dRGB[1];
-        dsh[3 * i + 2] = b * dRGB[2];
+      if (SHV > 0) {
+        // basis[] is zero beyond the active degree
+        float o[SHV > 0 ? SHV * 3 : 4];
+#pragma unroll
+        for (int i = 0; i < SHV; ++i) {
+          o[3 * i + 0] = basis[i] * dRGB[0];
+          o[3 * i + 1] = basis[i] * dRGB[1];
+          o[3 * i + 2] = basis[i] * dRGB[2];
+        }
+        float4* d4 = reinterpret_cast<float4*>(dsh);
+#pragma unroll
+        for (int i = 0; i < SHV * 3 / 4; ++i)
+          d4[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+      } else {
+        const int active = (Deg + 1) * (Deg + 1);
+        for (int i = 0; i < a.M; ++i) {
+          const float b = (i < active && i < 16) ? basis[i] : 0.f;
+          dsh[3 * i + 0] = b * dRGB[0];
+          dsh[3 * i + 1] = b * dRGB[1];
+          dsh[3 * i + 2] = b * dRGB[2];
+        }
       }
       const float3 dL_ddir = {dx[0] * dRGB[0] + dx[1] * dRGB[1] + dx[2] * dRGB[2],
                               dy[0] * dRGB[0] + dy[1] * dRGB[1] + dy[2] * dRGB[2],
@@ -435,13 +469,20 @@ int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dcampos, 0, 3 * sizeof(float), stream));
   if (a.P <= 0) return SOAR_OK;
   const int grid = ceil_div(a.P, 256);
+  const bool aligned = a.shs != nullptr && a.g.dL_dsh != nullptr &&
+                       ((reinterpret_cast<uintptr_t>(a.shs) | reinterpret_cast<uintptr_t>(a.g.dL_dsh)) & 15u) == 0;
+  const int shv = (aligned && a.M == 16) ? 16 : (aligned && a.M == 4 ? 4 : 0);
   {
     KernelScope ks(K_GEOM_BWD, stream);
-    geom_bwd_kernel<false><<<grid, 256, 0, stream>>>(a);
+    if (shv == 16) geom_bwd_kernel<false, 16><<<grid, 256, 0, stream>>>(a);
+    else if (shv == 4) geom_bwd_kernel<false, 4><<<grid, 256, 0, stream>>>(a);
+    else geom_bwd_kernel<false, 0><<<grid, 256, 0, stream>>>(a);
   }
   {
     KernelScope ks(K_GEOM_BWD, stream);
-    geom_bwd_kernel<true><<<grid, 256, 0, stream>>>(a);
+    if (shv == 16) geom_bwd_kernel<true, 16><<<grid, 256, 0, stream>>>(a);
+    else if (shv == 4) geom_bwd_kernel<true, 4><<<grid, 256, 0, stream>>>(a);
+    else geom_bwd_kernel<true, 0><<<grid, 256, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("geom_bwd_kernel");
   return SOAR_OK;

@@ -17,6 +17,8 @@
 namespace soar {
 
 
+// SHV: SH coefficients per Gaussian fetched with 16-byte loads (16 or 4); 0 = scalar path.
+template <int SHV>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
@@ -107,7 +109,19 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArg
   float rgb[3];
   if (a.colors_precomp == nullptr) {
     float3 cam = {a.campos[0], a.campos[1], a.campos[2]};
-    sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, p_orig, cam, rgb);
+    if (SHV > 0) {
+      float sh_local[SHV > 0 ? SHV * 3 : 4];
+      const float4* s4 = reinterpret_cast<const float4*>(a.shs + (size_t)idx * SHV * 3);
+#pragma unroll
+      for (int i = 0; i < SHV * 3 / 4; ++i) {
+        const float4 t = __ldg(s4 + i);
+        sh_local[4 * i + 0] = t.x; sh_local[4 * i + 1] = t.y;
+        sh_local[4 * i + 2] = t.z; sh_local[4 * i + 3] = t.w;
+      }
+      sh_to_rgb(SHV == 4 ? min(a.D, 1) : a.D, sh_local, p_orig, cam, rgb);
+    } else {
+      sh_to_rgb(a.D, a.shs + (size_t)idx * a.M * 3, p_orig, cam, rgb);
+    }
   } else {
     rgb[0] = a.colors_precomp[3 * idx];
     rgb[1] = a.colors_precomp[3 * idx + 1];
@@ -144,7 +158,10 @@ int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream) {
   if (a.P <= 0) return SOAR_OK;
   {
     KernelScope ks(K_PREPROCESS, stream);
-    preprocess_fwd_kernel<<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+    const bool aligned = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
+    if (aligned && a.M == 16) preprocess_fwd_kernel<16><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+    else if (aligned && a.M == 4) preprocess_fwd_kernel<4><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+    else preprocess_fwd_kernel<0><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return SOAR_OK;
