@@ -187,6 +187,7 @@ duplicate_tiles_kernel(int P, const float* __restrict__ records, const uint32_t*
     // pad lanes: start at the end of the warp's run so the search never selects them early
     start = 0xffffffffu;
   }
+  const uint32_t magic = w > 1 ? 0xffffffffu / w + 1u : 0u;  // floor(2^32 / w) + 1 (w == 1: row = r)
   const uint32_t run_begin = __shfl_sync(0xffffffffu, start, 0);
   // end of the run = start + tt of the last valid lane
   uint32_t endv = (k < P) ? start + tt : 0u;
@@ -207,10 +208,14 @@ duplicate_tiles_kernel(int P, const float* __restrict__ records, const uint32_t*
     const uint32_t o_start = __shfl_sync(0xffffffffu, start, j);
     const uint32_t o_xy0 = __shfl_sync(0xffffffffu, xy0, j);
     const uint32_t o_w = __shfl_sync(0xffffffffu, w, j);
+    const uint32_t o_magic = __shfl_sync(0xffffffffu, magic, j);
     const uint32_t o_idx = __shfl_sync(0xffffffffu, idx, j);
     if (slot < run_end) {
       const uint32_t r = slot - o_start;
-      const uint32_t row = r / o_w, col = r - row * o_w;
+      // r / o_w with the owner's reciprocal: the estimate is exact or one too large
+      uint32_t row = o_w > 1 ? __umulhi(r, o_magic) : r;
+      if (row * o_w > r) --row;
+      const uint32_t col = r - row * o_w;
       const uint32_t tile = ((o_xy0 >> 16) + row) * grid_x + (o_xy0 & 0xffffu) + col;
       keys[slot] = tile;
       values[slot] = o_idx;
@@ -256,7 +261,16 @@ constexpr uint32_t RS_FLAG_AGG = 1u << 30;
 constexpr uint32_t RS_FLAG_INCL = 2u << 30;
 constexpr uint32_t RS_FLAG_MASK = 3u << 30;
 constexpr uint32_t RS_VALUE_MASK = (1u << 30) - 1u;
+// tools/sort_probe.cu compiles this file with SOAR_SORT_PROBE to ablate stages of the pass
+#ifdef SOAR_SORT_PROBE
+__constant__ int g_probe;
+#define SORT_PROBE(bit) ((g_probe >> (bit)) & 1)
+#else
+#define SORT_PROBE(bit) 0
+#endif
 constexpr int RS_LB = 8;  // look-back words in flight per step
+constexpr size_t SORT_SMEM_BYTES =
+    (2 * (size_t)SORT_TILE + (SORT_THREADS / 32) * SORT_RADIX + 2 * SORT_RADIX + SORT_THREADS / 32 + 4) * 4;
 
 // One pass over the keys builds the digit histograms of every pass.
 __global__ void __launch_bounds__(256)
@@ -305,15 +319,19 @@ __global__ void __launch_bounds__(SORT_RADIX) radix_hist_scan_kernel(uint32_t* g
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                       const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                      uint32_t n, int shift, uint32_t digit_mask, uint32_t flip,
+                      uint32_t n, int shift, int nbits, uint32_t flip,
                       const uint32_t* __restrict__ ghist_excl, uint32_t* status, uint32_t* ticket) {
-  __shared__ uint32_t s_keys[SORT_TILE];
-  __shared__ uint32_t s_vals[SORT_TILE];
-  __shared__ uint32_t s_warp_hist[SORT_THREADS / 32][SORT_RADIX];
-  __shared__ uint32_t s_gofs[SORT_RADIX];
-  __shared__ uint32_t s_digit_excl[SORT_RADIX];
-  __shared__ uint32_t s_scan[SORT_THREADS / 32];
-  __shared__ uint32_t s_tile;
+  const uint32_t digit_mask = (1u << nbits) - 1u;
+  // dynamic shared memory (> 48 KB): keys | vals | per-warp digit histograms | offsets
+  extern __shared__ uint32_t s_dyn[];
+  uint32_t* const s_keys = s_dyn;
+  uint32_t* const s_vals = s_keys + SORT_TILE;
+  uint32_t (*const s_warp_hist)[SORT_RADIX] =
+      reinterpret_cast<uint32_t (*)[SORT_RADIX]>(s_vals + SORT_TILE);
+  uint32_t* const s_gofs = s_vals + SORT_TILE + (SORT_THREADS / 32) * SORT_RADIX;
+  uint32_t* const s_digit_excl = s_gofs + SORT_RADIX;
+  uint32_t* const s_scan = s_digit_excl + SORT_RADIX;
+  uint32_t& s_tile = s_scan[SORT_THREADS / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int NWARPS = SORT_THREADS / 32;
@@ -327,6 +345,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
 
   // ---- load (warp-striped inside each warp's contiguous chunk) and rank ----------
   uint32_t key[SORT_ITEMS];
+  uint32_t val[SORT_ITEMS];
   uint32_t rank[SORT_ITEMS];
   const uint32_t warp_base = warp * (32 * SORT_ITEMS);
 #pragma unroll
@@ -334,16 +353,40 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
     const uint32_t local = warp_base + j * 32 + lane;
     key[j] = (local < n_valid) ? keys_in[tile_base + local] : (~0u ^ flip);
   }
+  // values are fetched now so their latency hides behind the ranking
+#pragma unroll
+  for (int j = 0; j < SORT_ITEMS; ++j) {
+    const uint32_t local = warp_base + j * 32 + lane;
+    val[j] = tile_base + local;
+    if (vals_in != nullptr && local < n_valid) val[j] = vals_in[tile_base + local];
+  }
+  const uint32_t my_ghist = ghist_excl[tid];  // digit tid (SORT_THREADS == SORT_RADIX)
   const uint32_t lt_mask = lanemask_lt();
+  // Rank of a key among the warp's keys with the same digit = (count in earlier items) + (lanes
+  // below in this item). The per-digit running count lives in shared memory; the first lane of
+  // each peer group bumps it with ONE atomic whose return value is broadcast, so the twelve
+  // items only depend on each other through same-address atomic ordering, not through
+  // load/sync/store round trips.
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
     const uint32_t d = ((key[j] ^ flip) >> shift) & digit_mask;
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    if (SORT_PROBE(1)) { rank[j] = j; continue; }
+    // lanes holding the same digit: one ballot per digit bit (constant time; match.any
+    // serialises over the distinct values in the warp)
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < SORT_RADIX_BITS; ++b) {
+      if (b < nbits) {  // uniform: short last digits (e.g. 5 tile bits) cost 5 ballots
+        const bool bit = (d >> b) & 1u;
+        const uint32_t bal = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? bal : ~bal;
+      }
+    }
     const uint32_t lt = __popc(peers & lt_mask);
-    const uint32_t pre = s_warp_hist[warp][d];
-    __syncwarp();
-    if (lt == 0) s_warp_hist[warp][d] = pre + __popc(peers);
-    __syncwarp();
+    const int leader = __ffs(peers) - 1;
+    uint32_t pre = 0;
+    if (lt == 0) pre = atomicAdd(&s_warp_hist[warp][d], (uint32_t)__popc(peers));
+    pre = __shfl_sync(0xffffffffu, pre, leader);
     rank[j] = pre + lt;
   }
   __syncthreads();
@@ -380,7 +423,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
     // decoupled look-back over predecessor tiles for this digit; RS_LB status words are
     // fetched per step so the chain costs one L2 round trip per RS_LB tiles, not per tile
     uint32_t prev = 0;
-    if (tile != 0) {
+    if (tile != 0 && !SORT_PROBE(0)) {
       int t = (int)tile - 1;
       bool found = false;
       while (!found) {
@@ -403,7 +446,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
       }
       st_relaxed_u32(my_status, RS_FLAG_INCL | ((prev + total) & RS_VALUE_MASK));
     }
-    s_gofs[d] = ghist_excl[d] + prev - digit_excl;
+    s_gofs[d] = my_ghist + prev - digit_excl;
   }
   __syncthreads();
 
@@ -418,7 +461,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
 #pragma unroll
   for (int j = 0; j < SORT_ITEMS; ++j) {
     const uint32_t local = warp_base + j * 32 + lane;
-    if (local < n_valid) s_vals[rank[j]] = vals_in ? vals_in[tile_base + local] : tile_base + local;
+    if (local < n_valid) s_vals[rank[j]] = val[j];
   }
   __syncthreads();
 #pragma unroll
@@ -471,15 +514,18 @@ int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int en
   }
   SOAR_LAUNCH_CHECK("radix_hist_scan_kernel");
   uint32_t* tickets = status + (size_t)passes * n_sort_tiles * SORT_RADIX;
+  // per device and idempotent (a host-side attribute write, no device work)
+  SOAR_CUDA_TRY(cudaFuncSetAttribute(radix_onesweep_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)SORT_SMEM_BYTES));
   for (int p = 0; p < passes; ++p) {
     const int shift = p * SORT_RADIX_BITS;
     const int bits = min(SORT_RADIX_BITS, end_bit - shift);
-    const uint32_t mask = (1u << bits) - 1u;
     {
       KernelScope ks(K_RADIX_ONESWEEP, stream);
-      radix_onesweep_kernel<<<tiles, SORT_THREADS, 0, stream>>>(
+      radix_onesweep_kernel<<<tiles, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
           keys[p & 1], keys[(p + 1) & 1], (p == 0 && iota_values) ? nullptr : values[p & 1],
-          values[(p + 1) & 1], n, shift, mask, flip, ghist + p * SORT_RADIX,
+          values[(p + 1) & 1], n, shift, bits, flip, ghist + p * SORT_RADIX,
           status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
     }
     SOAR_LAUNCH_CHECK("radix_onesweep_kernel");
@@ -493,19 +539,33 @@ int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int en
 // =================================================================================
 __global__ void __launch_bounds__(256)
 tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges) {
-  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= L) return;
-  const uint32_t cur = keys[idx];
-  if (idx == 0) {
-    ranges[cur].x = 0;
+  // four consecutive list entries per thread (one 16-byte load) + the entry before them
+  const uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+  if (base >= L) return;
+  uint32_t k[4];
+  if (base + 4 <= L) {
+    const uint4 v = *reinterpret_cast<const uint4*>(keys + base);
+    k[0] = v.x; k[1] = v.y; k[2] = v.z; k[3] = v.w;
   } else {
-    const uint32_t prev = keys[idx - 1];
-    if (cur != prev) {
-      ranges[prev].y = idx;
-      ranges[cur].x = idx;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) k[i] = base + i < L ? keys[base + i] : 0u;
+  }
+  uint32_t prev = base > 0 ? keys[base - 1] : 0u;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t idx = base + i;
+    if (idx < L) {
+      const uint32_t cur = k[i];
+      if (idx == 0) {
+        ranges[cur].x = 0;
+      } else if (cur != prev) {
+        ranges[prev].y = idx;
+        ranges[cur].x = idx;
+      }
+      if (idx == L - 1) ranges[cur].y = L;
+      prev = cur;
     }
   }
-  if (idx == L - 1) ranges[cur].y = L;
 }
 
 int launch_tile_ranges(uint32_t L, const uint32_t* keys, uint2* ranges, int n_tiles,
@@ -514,7 +574,7 @@ int launch_tile_ranges(uint32_t L, const uint32_t* keys, uint2* ranges, int n_ti
   if (L == 0) return SOAR_OK;
   {
     KernelScope ks(K_TILE_RANGES, stream);
-    tile_ranges_kernel<<<ceil_div((int)L, 256), 256, 0, stream>>>(L, keys, ranges);
+    tile_ranges_kernel<<<ceil_div(ceil_div((int)L, 4), 256), 256, 0, stream>>>(L, keys, ranges);
   }
   SOAR_LAUNCH_CHECK("tile_ranges_kernel");
   return SOAR_OK;

@@ -6,9 +6,13 @@ TAG="${1:-rXX}"
 OUT=gpurun_out
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > $OUT/${TAG}_smi.csv 2>&1
+if [ "${SKIP_TESTS:-0}" != "1" ]; then
 python -m pytest tests -m gpu -x -q -rA > $OUT/${TAG}_gpu_tests.log 2>&1; echo "pytest exit $?" | tee -a $OUT/${TAG}_gpu_tests.log
 tail -3 $OUT/${TAG}_gpu_tests.log
+fi
+if [ "${SKIP_REF:-0}" != "1" ]; then
 python bench.py --impl reference --steps 10 --warmup 3 > $OUT/${TAG}_bench_reference.json 2> $OUT/${TAG}_bench_reference.err; echo "ref bench exit $?"
+fi
 python bench.py --steps 20 --warmup 5 > $OUT/${TAG}_bench_soar.json 2> $OUT/${TAG}_bench_soar.err; echo "soar bench exit $?"
 cat $OUT/${TAG}_bench_reference.json $OUT/${TAG}_bench_soar.json
 if [ "${SKIP_NCU:-0}" != "1" ]; then
@@ -18,7 +22,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 ncu --set full --clock-control none --import-source on \
-    -k regex:'blend_bwd_kernel|blend_fwd_kernel|onesweep|duplicate|geom_bwd|preprocess_fwd' -s 84 -c 12 \
+    -k regex:"${NCU_REGEX:-blend_bwd_kernel|blend_fwd_kernel|onesweep|duplicate|geom_bwd|preprocess_fwd}" -s ${NCU_SKIP:-84} -c ${NCU_COUNT:-12} \
     -o $OUT/${TAG}_prof -f $SHORT > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 fi
