@@ -72,6 +72,56 @@ __device__ __forceinline__ float warp_reduce16(float (&v)[16], uint32_t lane) {
   return v[0];
 }
 
+// In-kernel slot order of the per-(pixel, Gaussian) partials. The six dL/ddist moments
+// (sum of dd, dd*dx, dd*dy, dd*dx^2, dd*dx*dy, dd*dy^2 with d = centre - pixel) replace the
+// reference's five mean2D/conic sums: they are cheaper to form per pixel and are turned into
+// dL/dmean2D and dL/dconic once per (tile, Gaussian) at flush time. Variants without surface
+// normals only carry the first 10 slots (12-shuffle reduction instead of 16).
+enum LocalSlot {
+  LS_DC0 = 0, LS_DC1 = 1, LS_DC2 = 2, LS_DD = 3, LS_DO = 4, LS_MX = 5, LS_MY = 6, LS_MXX = 7,
+  LS_MXY = 8, LS_MYY = 9, LS_DN0 = 10, LS_DN1 = 11, LS_DN2 = 12, LS_GD = 13, LS_COUNT = 14
+};
+
+// Sum v[0..9] over the 32 lanes with 12 shuffles. Returns the total of slot `idx` (output);
+// idx < 0 on lanes that hold a duplicate.
+__device__ __forceinline__ float warp_reduce10(float (&v)[16], uint32_t lane, int& idx) {
+  const bool h4 = lane & 16, h3 = lane & 8, h2 = lane & 4, h1 = lane & 2;
+  // xor 16: pairs (i, i+5)
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const float send = h4 ? v[i] : v[i + 5];
+    const float keep = h4 ? v[i + 5] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+  // xor 8: pairs (0,3) (1,4); 2 is summed in place
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const float send = h3 ? v[i] : v[i + 3];
+    const float keep = h3 ? v[i + 3] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+  v[2] += __shfl_xor_sync(0xffffffffu, v[2], 8);
+  // xor 4: pair (0,1); 2 in place
+  {
+    const float send = h2 ? v[0] : v[1];
+    const float keep = h2 ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  v[2] += __shfl_xor_sync(0xffffffffu, v[2], 4);
+  // xor 2: pair (0,2)
+  {
+    const float send = h1 ? v[0] : v[2];
+    const float keep = h1 ? v[2] : v[0];
+    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  }
+  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+  const int base = h4 ? 5 : 0;
+  if (!h1) idx = base + (h3 ? 3 : 0) + (h2 ? 1 : 0);
+  else idx = (!h3 && !h2) ? base + 2 : -1;
+  if (lane & 1) idx = -1;
+  return v[0];
+}
+
 struct BlendBwdSmem {
   float4 q0[BWD_BATCH];  // x y conA conB
   float4 q1[BWD_BATCH];  // conC opac thr depth
@@ -106,13 +156,13 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   const float D_final = inside && NORM_DEPTH ? a.final_D[pix_id] : 0;
   const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0;
 
-  // deepest contributor of the tile: nothing behind it receives a gradient
-  {
-    uint32_t m = last_contributor;
+  // deepest contributor of the tile (and of this warp's block): nothing behind it receives
+  // a gradient
+  uint32_t block_depth = last_contributor;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) sm.max_contrib[warp] = m;
-  }
+  for (int o = 16; o > 0; o >>= 1)
+    block_depth = max(block_depth, __shfl_xor_sync(0xffffffffu, block_depth, o));
+  if (lane == 0) sm.max_contrib[warp] = block_depth;
 #pragma unroll
   for (int k = 0; k < GACC_FLOATS; ++k) sm.acc[tid][k] = 0.f;
   __syncthreads();
@@ -193,7 +243,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
 
     for (uint32_t c0 = 0; c0 < n; c0 += 32) {
       const uint32_t jj = c0 + lane;
-      const bool mine = jj < n && ((sm.mask[jj] >> warp) & 1u);
+      const bool mine = jj < n && ((sm.mask[jj] >> warp) & 1u) && sm.pos[jj] < block_depth;
       uint32_t bits = __ballot_sync(0xffffffffu, mine);
       while (bits) {
         const uint32_t j = c0 + __ffs(bits) - 1;
@@ -206,7 +256,9 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
         const float power = -0.5f * dist;
         live = live && !(power > 0.0f) && !(power < q1j.z);
         if (!__any_sync(0xffffffffu, live)) continue;
-        const float G = exp(power);
+        // the backward is compared at 1e-3 relative (the reference's own atomics are unordered):
+        // fast exp2-based exponential and reciprocal are far inside that
+        const float G = __expf(power);
         const float alpha = min(0.99f, q1j.y * G);
         live = live && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, live)) continue;
@@ -217,7 +269,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
 
         if (live) {
           const float T_behind = T;  // transmittance after this Gaussian (front-to-back)
-          const float rcp = __frcp_rn(1.f - alpha);
+          const float rcp = __fdividef(1.f, 1.f - alpha);
           T = T * rcp;
           const float dchannel_dcolor = alpha * T;
           const float4 q2 = sm.q2[j];
@@ -228,31 +280,26 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           // linear, so S = sum_ch g_ch * accum_rec_ch is carried as ONE scalar:
           // S <- last_alpha * cg_last + (1 - last_alpha) * S, cg = sum_ch g_ch * c_ch.
           float cg = q2.x * dL_dpixC[0] + q2.y * dL_dpixC[1] + q2.z * dL_dpixC[2];
-          v[GA_DC0 + 0] = dchannel_dcolor * dL_dpixC[0];
-          v[GA_DC0 + 1] = dchannel_dcolor * dL_dpixC[1];
-          v[GA_DC0 + 2] = dchannel_dcolor * dL_dpixC[2];
-          float J6 = 0.f, J9 = 0.f;
-          float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          v[LS_DC0] = dchannel_dcolor * dL_dpixC[0];
+          v[LS_DC1] = dchannel_dcolor * dL_dpixC[1];
+          v[LS_DC2] = dchannel_dcolor * dL_dpixC[2];
+          float d_cur = q1j.w;
           if (SURFACE) {
             const float4 q3 = sm.q3[j];
             cg += q3.x * dL_dpixN[0] + q3.y * dL_dpixN[1] + q3.z * dL_dpixN[2];
-            v[GA_DN0 + 0] = dchannel_dcolor * dL_dpixN[0] * 10;
-            v[GA_DN0 + 1] = dchannel_dcolor * dL_dpixN[1] * 10;
-            v[GA_DN0 + 2] = dchannel_dcolor * dL_dpixN[2] * 10;
+            v[LS_DN0] = dchannel_dcolor * dL_dpixN[0] * 10;
+            v[LS_DN1] = dchannel_dcolor * dL_dpixN[1] * 10;
+            v[LS_DN2] = dchannel_dcolor * dL_dpixN[2] * 10;
             if (DEPTH_DIFF) {
-              J6 = q2.w;
-              J9 = q3.w;
-              q4 = sm.q4[j];
+              const float4 q4 = sm.q4[j];
+              const float dif_u0 = d.x * q4.x + d.y * q4.y;
+              const float dif_u1 = d.x * q4.z + d.y * q4.w;
+              d_cur -= dif_u0 * q2.w + dif_u1 * q3.w;
+              v[LS_GD] = dL_dpixD;  // the pixel-depth term of dL/dmean2D is formed at flush
             }
           }
-          float d_cur = q1j.w;
-          if (DEPTH_DIFF) {
-            const float dif_u0 = d.x * q4.x + d.y * q4.y;
-            const float dif_u1 = d.x * q4.z + d.y * q4.w;
-            d_cur -= dif_u0 * J6 + dif_u1 * J9;
-          }
           cg += d_cur * dL_ddepth_ch;
-          v[GA_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
+          v[LS_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
           S = last_alpha * cg_last + (1.f - last_alpha) * S;
           cg_last = cg;
           float dL_dalpha = cg - S;
@@ -261,41 +308,56 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           dL_dalpha += tf_k * rcp;
           last_alpha = alpha;
 
-          const float dL_ddist = dL_dalpha * q1j.y * -0.5f * G;
-          float ndc_x = dL_ddist * 2 * (q0j.z * d.x + q0j.w * d.y) * ddelx_dx;
-          float ndc_y = dL_ddist * 2 * (q1j.x * d.y + q0j.w * d.x) * ddely_dy;
-          if (DEPTH_DIFF) {
-            ndc_x += 1 * -dL_dpixD * (J6 * q4.x + J9 * q4.z);
-            ndc_y += 1 * -dL_dpixD * (J6 * q4.y + J9 * q4.w);
-          }
-          v[GA_DMX] = ndc_x;
-          v[GA_DMY] = ndc_y;
-          v[GA_DCA] = dL_ddist * (d.x * d.x);
-          v[GA_DCB] = dL_ddist * (1 * d.x * d.y);
-          v[GA_DCC] = dL_ddist * (d.y * d.y);
-          v[GA_DO] = G * dL_dalpha;
+          const float gda = G * dL_dalpha;
+          const float dL_ddist = gda * q1j.y * -0.5f;
+          const float ddx = dL_ddist * d.x, ddy = dL_ddist * d.y;
+          v[LS_DO] = gda;
+          v[LS_MX] = ddx;
+          v[LS_MY] = ddy;
+          v[LS_MXX] = ddx * d.x;
+          v[LS_MXY] = ddx * d.y;
+          v[LS_MYY] = ddy * d.y;
         }
 
-        const float total = warp_reduce16(v, lane);
-        if ((lane & 1) == 0 && (lane >> 1) < 13) atomicAdd(&sm.acc[j][lane >> 1], total);
+        if (SURFACE) {
+          const float total = warp_reduce16(v, lane);
+          if ((lane & 1) == 0 && (lane >> 1) < LS_COUNT) atomicAdd(&sm.acc[j][lane >> 1], total);
+        } else {
+          int slot_idx;
+          const float total = warp_reduce10(v, lane, slot_idx);
+          if (slot_idx >= 0) atomicAdd(&sm.acc[j][slot_idx], total);
+        }
       }
     }
     __syncthreads();
 
-    // flush this batch: thread t owns compacted entry t
+    // flush this batch: thread t owns compacted entry t and turns its moment sums into the
+    // reference's 13 per-Gaussian partials (backward.cu:820-855)
     if ((uint32_t)tid < n) {
       float* acc = sm.acc[tid];
       bool any = false;
 #pragma unroll
-      for (int k = 0; k < 13; ++k) any = any || (acc[k] != 0.f);
+      for (int k = 0; k < LS_COUNT; ++k) any = any || (acc[k] != 0.f);
       if (any) {
+        const float4 e0 = sm.q0[tid], e1 = sm.q1[tid];
+        const float cA = e0.z, cB = e0.w, cC = e1.x;
+        const float mx = acc[LS_MX], my = acc[LS_MY];
+        float ndc_x = 2 * (cA * mx + cB * my) * ddelx_dx;
+        float ndc_y = 2 * (cC * my + cB * mx) * ddely_dy;
+        if (DEPTH_DIFF) {
+          const float4 e4 = sm.q4[tid];
+          const float J6 = sm.q2[tid].w, J9 = sm.q3[tid].w;
+          ndc_x += -acc[LS_GD] * (J6 * e4.x + J9 * e4.z);
+          ndc_y += -acc[LS_GD] * (J6 * e4.y + J9 * e4.w);
+        }
         float* g = a.gacc + (size_t)sm.id[tid] * GACC_FLOATS;
-        red_add_v4(g + 0, acc[0], acc[1], acc[2], acc[3]);
-        red_add_v4(g + 4, acc[4], acc[5], acc[6], acc[7]);
-        red_add_v4(g + 8, acc[8], acc[9], acc[10], acc[11]);
-        atomicAdd(g + 12, acc[12]);
+        // GA_* order: dcolor[3] dnormal[3] ddepth dmean2D.xy dconic.(a,b,c) dopacity
+        red_add_v4(g + 0, acc[LS_DC0], acc[LS_DC1], acc[LS_DC2], SURFACE ? acc[LS_DN0] : 0.f);
+        red_add_v4(g + 4, SURFACE ? acc[LS_DN1] : 0.f, SURFACE ? acc[LS_DN2] : 0.f, acc[LS_DD], ndc_x);
+        red_add_v4(g + 8, ndc_y, acc[LS_MXX], acc[LS_MXY], acc[LS_MYY]);
+        atomicAdd(g + 12, acc[LS_DO]);
 #pragma unroll
-        for (int k = 0; k < 13; ++k) acc[k] = 0.f;
+        for (int k = 0; k < LS_COUNT; ++k) acc[k] = 0.f;
       }
     }
     // the next round's staging writes happen after its first barrier; the flush above only
