@@ -224,6 +224,8 @@ int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
   b.n_contrib = reinterpret_cast<uint32_t*>(at(img, IL.n_contrib));
   b.final_D = reinterpret_cast<float*>(at(img, IL.final_D));
   b.out_color = out_color; b.out_normal = out_normal; b.out_depth = out_depth; b.out_opac = out_opac;
+  // the ping-pong half the sort left free holds one block-mask byte per list entry
+  b.pair_mask = reinterpret_cast<uint8_t*>(keys[sorted ^ 1]);
   return launch_blend_fwd(b, d.grid_y, stream);
 }
 
@@ -279,6 +281,7 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
       b.dL_dpixcolor = dL_dout_color; b.dL_dpixnormal = dL_dout_normal;
       b.dL_dpixdepth = dL_dout_depth; b.dL_dpixopac = dL_dout_opac;
       b.gacc = gacc;
+      b.pair_mask = reinterpret_cast<const uint8_t*>(at(binning, BL.keys[sorted ^ 1]));
       rc = launch_blend_bwd(b, d.grid_y, stream);
       if (rc) return rc;
     }

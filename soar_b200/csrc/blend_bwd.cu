@@ -14,7 +14,8 @@
 //   * the replay starts at the tile's deepest n_contrib instead of the end of its range;
 //   * list entries that cannot reach alpha >= 1/255 anywhere in the tile are dropped at
 //     staging time, and every warp (an 8x4 pixel block) only visits the entries whose
-//     footprint can touch its block (blend_common.cuh);
+//     footprint can touch its block (blend_common.cuh); the block masks are the bytes the
+//     forward blend left in the binning buffer, so a culled entry costs a one-byte load;
 //   * pixel-constant factors are hoisted, 1/(1-alpha) is formed once per contribution, and
 //     the body is specialised on (surface, per-pixel depth, normalize_depth).
 #include "common.cuh"
@@ -146,7 +147,6 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   const bool inside = px < (uint32_t)a.W && py < (uint32_t)a.H;
   const uint32_t pix_id = (uint32_t)a.W * py + px;
   const float2 pixf = {(float)px, (float)py};
-  const float tile_px = (float)(tile_x * TILE_X), tile_py = (float)(tile_y * TILE_Y);
   const size_t HW = (size_t)a.H * a.W;
 
   const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
@@ -213,11 +213,15 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
     const float4* rec = nullptr;
     float4 q0, q1;
     if (progress < tile_depth) {
-      id = a.point_list[list_end - progress - 1];
-      rec = reinterpret_cast<const float4*>(a.records + (size_t)id * REC_FLOATS);
-      q0 = __ldg(rec + 0);
-      q1 = __ldg(rec + 1);
-      mask = tile_block_mask(q0, q1, tile_px, tile_py);
+      // every entry in front of the tile's deepest contributor was staged by the forward,
+      // which left its block mask behind: culled entries cost one byte here
+      mask = a.pair_mask[list_end - progress - 1];
+      if (mask != 0) {
+        id = a.point_list[list_end - progress - 1];
+        rec = reinterpret_cast<const float4*>(a.records + (size_t)id * REC_FLOATS);
+        q0 = __ldg(rec + 0);
+        q1 = __ldg(rec + 1);
+      }
     }
     const uint32_t keep_ballot = __ballot_sync(0xffffffffu, mask != 0);
     if (lane == 0) sm.wcount[warp] = __popc(keep_ballot);

@@ -59,6 +59,7 @@ struct BlendFwdArgs {
   float* out_normal;
   float* out_depth;
   float* out_opac;
+  uint8_t* pair_mask;  // [R] block mask of every staged list entry (read back by the backward)
 };
 int launch_blend_fwd(const BlendFwdArgs& a, int grid_y, cudaStream_t stream);
 
@@ -77,6 +78,7 @@ struct BlendBwdArgs {
   const float* dL_dpixdepth;
   const float* dL_dpixopac;
   float* gacc;
+  const uint8_t* pair_mask;  // [R] written by the forward blend of the same view
 };
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream);
 

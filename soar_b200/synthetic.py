@@ -177,3 +177,55 @@ def skinning_problem(N, seed=0):
     q = rng.normal(size=(N, 4))
     q /= np.linalg.norm(q, axis=1, keepdims=True)
     return dict(points=_t(pts), quats=_t(q), weights=_t(w), bones=_t(A))
+
+
+def _skeleton(rng):
+    """55 rest-pose joint positions of a capsule humanoid along the SMPL-X kinematic tree."""
+    J = N_JOINTS
+    joints = np.zeros((J, 3))
+    for j in range(1, J):
+        p = SMPLX_PARENTS[j]
+        step = rng.normal(size=3)
+        step[1] = -abs(step[1]) if j in (1, 2, 4, 5, 7, 8, 10, 11) else abs(step[1])
+        step /= np.linalg.norm(step)
+        joints[j] = joints[p] + step * (0.12 if j < 22 else 0.03)
+    return joints
+
+
+def smplx_template(V=N_VERTS, NB=20, seed=0):
+    """SMPL-X-shaped body model with synthetic assets (§8d; the real SMPLX_*.npz are behind a
+    login): v_template [V,3] on capsules around the skeleton, shapedirs [V,3,NB] ~ N(0,0.01^2),
+    posedirs [(J-1)*9, V*3] ~ N(0,0.001^2), J_regressor [J,V] = row-normalised indicator of each
+    joint's 64 nearest vertices, parents [J], lbs_weights [V,J] = top-4 softmax(-d^2/0.08^2)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 4241))
+    J = N_JOINTS
+    joints = _skeleton(rng)
+    seg = rng.integers(1, J, size=V)
+    t = rng.uniform(size=(V, 1))
+    verts = joints[np.asarray(SMPLX_PARENTS)[seg]] * (1 - t) + joints[seg] * t
+    verts += rng.normal(scale=0.03, size=(V, 3))
+    d2 = ((verts[:, None, :] - joints[None]) ** 2).sum(-1)
+    logits = -d2 / (0.08 ** 2)
+    kth = np.partition(logits, -4, axis=1)[:, -4][:, None]
+    w = np.where(logits >= kth, np.exp(logits - logits.max(1, keepdims=True)), 0.0)
+    w /= w.sum(1, keepdims=True)
+    k = min(64, V)
+    near = np.argpartition(d2, k - 1, axis=0)[:k]  # [k, J]
+    Jreg = np.zeros((J, V))
+    for j in range(J):
+        Jreg[j, near[:, j]] = 1.0 / k
+    shapedirs = rng.normal(scale=0.01, size=(V, 3, NB))
+    posedirs = rng.normal(scale=0.001, size=((J - 1) * 9, V * 3))
+    return dict(v_template=_t(verts), shapedirs=_t(shapedirs), posedirs=_t(posedirs),
+                J_regressor=_t(Jreg), parents=torch.tensor(SMPLX_PARENTS, dtype=torch.int64),
+                lbs_weights=_t(w))
+
+
+def smplx_pose(NB=20, seed=0, global_orient_zero=True):
+    """betas [1,NB] ~ N(0,0.5^2), full_pose [1,165] axis-angles ~ N(0,0.3^2), transl (0,0.3,0)."""
+    rng = np.random.Generator(np.random.PCG64(seed + 90001))
+    betas = rng.normal(scale=0.5, size=(1, NB))
+    pose = rng.normal(scale=0.3, size=(N_JOINTS, 3))
+    if global_orient_zero:
+        pose[0] = 0.0
+    return dict(betas=_t(betas), full_pose=_t(pose.reshape(1, -1)), transl=_t([[0.0, 0.3, 0.0]]))
