@@ -146,8 +146,13 @@ class Workload:
         gen = torch.Generator().manual_seed(1234 + rank)
         self.tgt_host = [torch.rand((8, self.H, self.W), generator=gen).pin_memory()
                          for _ in range(min(CAMS_PER_RANK, views_per_rank * 2))]
-        self.tgt_dev = torch.empty((8, self.H, self.W), **f32)
-        self.cam_stage = torch.empty(35, **f32)
+        # e2e staging: double-buffered device copies filled by a side stream, so the host->device
+        # copy of view k+1 overlaps the render of view k (both inside the timed region)
+        self.tgt_dev = [torch.empty((8, self.H, self.W), **f32) for _ in range(2)]
+        self.cam_stage = [torch.empty(35, **f32) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=device)
+        self.copied = [torch.cuda.Event() for _ in range(2)]
+        self.consumed = [torch.cuda.Event() for _ in range(2)]
         self.loss_host = torch.zeros(1).pin_memory()
 
     def scene_dict(self, cam_flat):
@@ -263,14 +268,28 @@ def step_resident(arm, wl, step):
     wl.flat.allreduce()
 
 
+def _stage_view(wl, step, v, slot):
+    """Enqueue the host->device copy of view v's camera and target images on the copy stream."""
+    i = wl.view_index(step, v)
+    with torch.cuda.stream(wl.copy_stream):
+        wl.copy_stream.wait_event(wl.consumed[slot])  # the previous user of this slot is done
+        wl.cam_stage[slot].copy_(wl.cam_host[i], non_blocking=True)
+        wl.tgt_dev[slot].copy_(wl.tgt_host[i % len(wl.tgt_host)], non_blocking=True)
+        wl.copied[slot].record(wl.copy_stream)
+
+
 def step_e2e(arm, wl, step):
     wl.flat.zero_()
     total = None
+    main = torch.cuda.current_stream()
+    _stage_view(wl, step, 0, 0)
     for v in range(wl.vpr):
-        i = wl.view_index(step, v)
-        wl.cam_stage.copy_(wl.cam_host[i], non_blocking=True)
-        wl.tgt_dev.copy_(wl.tgt_host[i % len(wl.tgt_host)], non_blocking=True)
-        loss = arm.view_e2e(wl.cam_stage, wl.tgt_dev)
+        slot = v & 1
+        if v + 1 < wl.vpr:
+            _stage_view(wl, step, v + 1, slot ^ 1)
+        main.wait_event(wl.copied[slot])
+        loss = arm.view_e2e(wl.cam_stage[slot], wl.tgt_dev[slot])
+        wl.consumed[slot].record(main)
         total = loss if total is None else total + loss
     wl.flat.allreduce()
     wl.loss_host.copy_(total.reshape(1), non_blocking=True)

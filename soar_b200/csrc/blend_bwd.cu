@@ -27,6 +27,17 @@ namespace soar {
 
 constexpr int BWD_BATCH = TILE_PIX;
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
                "f"(d)
@@ -152,7 +163,8 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
   if (range.y == range.x) return;
 
-  const float T_final = inside ? a.final_T[pix_id] : 0;
+  // lanes outside the image never contribute; 0.5 keeps their (discarded) arithmetic finite
+  const float T_final = inside ? a.final_T[pix_id] : 0.5f;
   const float D_final = inside && NORM_DEPTH ? a.final_D[pix_id] : 0;
   const uint32_t last_contributor = inside ? a.n_contrib[pix_id] : 0;
 
@@ -261,19 +273,22 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
         live = live && !(power > 0.0f) && !(power < q1j.z);
         if (!__any_sync(0xffffffffu, live)) continue;
         // the backward is compared at 1e-3 relative (the reference's own atomics are unordered):
-        // fast exp2-based exponential and reciprocal are far inside that
-        const float G = __expf(power);
-        const float alpha = min(0.99f, q1j.y * G);
+        // single-instruction ex2 / rcp approximations (2^-22 relative) are far inside that
+        const float G = ex2_approx(power * 1.4426950408889634f);
+        float alpha = min(0.99f, q1j.y * G);
         live = live && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, live)) continue;
 
+        // Lanes that do not contribute run the same arithmetic with alpha = 0 and G = 0: T, S and
+        // every partial then come out unchanged / zero, so nothing below is predicated.
+        alpha = live ? alpha : 0.f;
+        const float Gl = live ? G : 0.f;
         float v[16];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) v[k] = 0.f;
-
-        if (live) {
+        for (int k = LS_COUNT; k < 16; ++k) v[k] = 0.f;
+        {
           const float T_behind = T;  // transmittance after this Gaussian (front-to-back)
-          const float rcp = __fdividef(1.f, 1.f - alpha);
+          const float rcp = rcp_approx(1.f - alpha);
           T = T * rcp;
           const float dchannel_dcolor = alpha * T;
           const float4 q2 = sm.q2[j];
@@ -288,6 +303,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           v[LS_DC1] = dchannel_dcolor * dL_dpixC[1];
           v[LS_DC2] = dchannel_dcolor * dL_dpixC[2];
           float d_cur = q1j.w;
+          v[LS_DN0] = v[LS_DN1] = v[LS_DN2] = v[LS_GD] = 0.f;
           if (SURFACE) {
             const float4 q3 = sm.q3[j];
             cg += q3.x * dL_dpixN[0] + q3.y * dL_dpixN[1] + q3.z * dL_dpixN[2];
@@ -299,7 +315,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
               const float dif_u0 = d.x * q4.x + d.y * q4.y;
               const float dif_u1 = d.x * q4.z + d.y * q4.w;
               d_cur -= dif_u0 * q2.w + dif_u1 * q3.w;
-              v[LS_GD] = dL_dpixD;  // the pixel-depth term of dL/dmean2D is formed at flush
+              v[LS_GD] = live ? dL_dpixD : 0.f;  // the pixel-depth term of dL/dmean2D is formed at flush
             }
           }
           cg += d_cur * dL_ddepth_ch;
@@ -312,7 +328,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           dL_dalpha += tf_k * rcp;
           last_alpha = alpha;
 
-          const float gda = G * dL_dalpha;
+          const float gda = Gl * dL_dalpha;
           const float dL_ddist = gda * q1j.y * -0.5f;
           const float ddx = dL_ddist * d.x, ddy = dL_ddist * d.y;
           v[LS_DO] = gda;
