@@ -166,6 +166,37 @@ int soar_lbs_backward(const float* mats, const float* quats, int32_t N, int32_t 
                       const float* dL_dout_points, const float* dL_dout_quats,
                       float* dL_dpoints, float* dL_dquats, soar_stream_t stream);
 
+/* Skin-weight query (replaces SMPL_Guidance.query_weights_smpl, TS/utils/smpl.py:618-637:
+ * pytorch3d.knn_points(K=30) + sqrt/clamp(1e-4, 1) + inverse-distance blend of the K nearest
+ * canonical vertices' skin-weight rows), optionally fused with the bone blend of :613.
+ * points[N,3], cano_vertices[V,3] (V <= 16384), lbs_weights[V,J] (J <= 64), K <= 32.
+ * out_weights[N,J] and/or out_mats[N,12] (needs bones[J,16]); either may be NULL, not both. */
+int soar_lbs_query_weights(const float* points, int32_t N, const float* cano_vertices, int32_t V,
+                           const float* lbs_weights, int32_t J, int32_t K, const float* bones,
+                           float* out_weights, float* out_mats, soar_stream_t stream);
+
+/* ---- SMPL-X body-model forward for one pose (replaces smplx.lbs.lbs(),
+ *      TS/utils/smplx/lbs.py:147-246, plus the transl fold of SMPLX.forward,
+ *      TS/utils/smplx/body_models.py:1380-1383, and the cano->live bones of
+ *      TS/utils/smpl.py:609) ---------------------------------------------------------- */
+typedef struct SoarSmplxModel {
+  int32_t V, J, NB;           /* vertices, joints (<= 64), shape coefficients (<= 64) */
+  const float* v_template;    /* [V,3]                                                */
+  const float* shapedirs;     /* [V,3,NB]                                             */
+  const float* posedirs;      /* [(J-1)*9, V*3]                                       */
+  const float* J_regressor;   /* [J,V]                                                */
+  const int32_t* parents;     /* [J], parents[0] ignored                              */
+  const float* lbs_weights;   /* [V,J]                                                */
+} SoarSmplxModel;
+size_t soar_smplx_workspace_bytes(int32_t V, int32_t J);
+/* betas[NB], full_pose[J*3] axis-angle, transl[3] or NULL, inv_mats[J,16] or NULL.
+ * Outputs (each may be NULL): out_verts[V,3], out_joints[J,3], out_A[J,16] with transl folded
+ * in (Q17), out_bones[J,16] = out_A . inv_mats. */
+int soar_smplx_forward(const SoarSmplxModel* model, const float* betas, const float* full_pose,
+                       const float* transl, const float* inv_mats, float* out_verts,
+                       float* out_joints, float* out_A, float* out_bones, void* workspace,
+                       size_t workspace_bytes, soar_stream_t stream);
+
 /* ---- launch accounting / event timing (used by bench.py; no reference analogue:
  *      the reference has an unused CUDA-event Timer, TS/utils/cuda_utils.cu:18-42) --- */
 /* Number of kernels this library has launched in this process. */

@@ -63,6 +63,20 @@ class SoarRastGrads(Structure):
     ]
 
 
+class SoarSmplxModel(Structure):
+    _fields_ = [
+        ("V", c_int32),
+        ("J", c_int32),
+        ("NB", c_int32),
+        ("v_template", c_void_p),
+        ("shapedirs", c_void_p),
+        ("posedirs", c_void_p),
+        ("J_regressor", c_void_p),
+        ("parents", c_void_p),
+        ("lbs_weights", c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); mirrors include/soar_b200.h one to one
 SIGNATURES = {
     "soar_rast_geom_bytes": (c_size_t, [c_int32]),
@@ -102,6 +116,17 @@ SIGNATURES = {
     "soar_lbs_backward": (
         c_int32,
         [c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_lbs_query_weights": (
+        c_int32,
+        [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
+         c_void_p, c_void_p],
+    ),
+    "soar_smplx_workspace_bytes": (c_size_t, [c_int32, c_int32]),
+    "soar_smplx_forward": (
+        c_int32,
+        [POINTER(SoarSmplxModel), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
     "soar_launch_count": (ctypes.c_ulonglong, []),
     "soar_prof_enable": (None, [c_int32]),

@@ -145,3 +145,212 @@ smplx_joints_kernel(const float* __restrict__ J_regressor, const float* __restri
   }
   if (threadIdx.x < 3) joints[3 * j + threadIdx.x] = s_red[threadIdx.x][0];
 }
+
+// ---- 4. kinematic chain (one CTA of SMPLX_MAX_J threads, thread j = joint j) ------------------
+// G[j] = G[parent] . [R_j | J_j - J_parent]; joints at the same depth are composed together.
+__global__ void __launch_bounds__(SMPLX_MAX_J)
+smplx_chain_kernel(const float* __restrict__ full_pose, const int32_t* __restrict__ parents,
+                   const float* __restrict__ joints, const float* __restrict__ transl,
+                   const float* __restrict__ inv_mats, int J, float* __restrict__ A_skin,
+                   float* __restrict__ out_joints, float* __restrict__ out_A,
+                   float* __restrict__ out_bones) {
+  __shared__ float s_G[SMPLX_MAX_J][12];  // rows 0..2 of the 4x4, row-major
+  __shared__ int s_depth[SMPLX_MAX_J];
+  __shared__ int s_maxdepth;
+  const int j = threadIdx.x;
+  float L[12];  // local transform
+  int parent = -1, depth = 0;
+  if (j < J) {
+    float R[9];
+    rodrigues(full_pose + 3 * j, R);
+    parent = j == 0 ? -1 : parents[j];
+    float t[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+      t[k] = joints[3 * j + k] - (parent >= 0 ? joints[3 * parent + k] : 0.f);
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      L[r * 4 + 0] = R[r * 3 + 0]; L[r * 4 + 1] = R[r * 3 + 1]; L[r * 4 + 2] = R[r * 3 + 2];
+      L[r * 4 + 3] = t[r];
+    }
+    for (int p = parent; p >= 0 && depth < SMPLX_MAX_J; p = (p == 0 ? -1 : parents[p])) ++depth;
+    s_depth[j] = depth;
+    if (depth == 0) {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) s_G[j][k] = L[k];
+    }
+  }
+  if (j == 0) s_maxdepth = 0;
+  __syncthreads();
+  if (j < J) atomicMax(&s_maxdepth, depth);
+  __syncthreads();
+  const int maxdepth = s_maxdepth;
+  for (int lvl = 1; lvl <= maxdepth; ++lvl) {
+    if (j < J && depth == lvl) {
+      const float* P = s_G[parent];
+      float G[12];
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float acc = P[r * 4 + 0] * L[0 * 4 + c] + P[r * 4 + 1] * L[1 * 4 + c] + P[r * 4 + 2] * L[2 * 4 + c];
+          if (c == 3) acc += P[r * 4 + 3];  // times the local's bottom-right 1
+          G[r * 4 + c] = acc;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 12; ++k) s_G[j][k] = G[k];
+    }
+    __syncthreads();
+  }
+  if (j >= J) return;
+  float G[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) G[k] = s_G[j][k];
+  const float tx = transl ? transl[0] : 0.f, ty = transl ? transl[1] : 0.f, tz = transl ? transl[2] : 0.f;
+  const float tr[3] = {tx, ty, tz};
+  float A[12];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float gj = G[r * 4 + 0] * joints[3 * j] + G[r * 4 + 1] * joints[3 * j + 1] + G[r * 4 + 2] * joints[3 * j + 2];
+    A[r * 4 + 0] = G[r * 4 + 0]; A[r * 4 + 1] = G[r * 4 + 1]; A[r * 4 + 2] = G[r * 4 + 2];
+    A[r * 4 + 3] = G[r * 4 + 3] - gj;
+    if (out_joints) out_joints[3 * j + r] = G[r * 4 + 3] + tr[r];
+  }
+#pragma unroll
+  for (int k = 0; k < 12; ++k) A_skin[12 * j + k] = A[k];
+#pragma unroll
+  for (int r = 0; r < 3; ++r) A[r * 4 + 3] += tr[r];
+  if (out_A) {
+#pragma unroll
+    for (int k = 0; k < 12; ++k) out_A[16 * j + k] = A[k];
+    out_A[16 * j + 12] = 0.f; out_A[16 * j + 13] = 0.f; out_A[16 * j + 14] = 0.f; out_A[16 * j + 15] = 1.f;
+  }
+  if (out_bones && inv_mats) {
+    const float* B = inv_mats + 16 * j;
+    const float Afull[16] = {A[0], A[1], A[2], A[3], A[4], A[5], A[6], A[7],
+                             A[8], A[9], A[10], A[11], 0.f, 0.f, 0.f, 1.f};
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c)
+        out_bones[16 * j + 4 * r + c] = Afull[4 * r + 0] * B[0 * 4 + c] + Afull[4 * r + 1] * B[1 * 4 + c] +
+                                        Afull[4 * r + 2] * B[2 * 4 + c] + Afull[4 * r + 3] * B[3 * 4 + c];
+  }
+}
+
+// ---- 5. vertex skinning --------------------------------------------------------------------
+__global__ void __launch_bounds__(SMPLX_THREADS)
+smplx_skin_kernel(const float* __restrict__ v_shaped, const float* __restrict__ partial,
+                  const float* __restrict__ lbs_weights, const float* __restrict__ A_skin,
+                  const float* __restrict__ transl, int V, int J, float* __restrict__ out_verts) {
+  __shared__ float s_A[SMPLX_MAX_J * 12];
+  for (int i = threadIdx.x; i < J * 12; i += SMPLX_THREADS) s_A[i] = A_skin[i];
+  __syncthreads();
+  const int v = blockIdx.x * SMPLX_THREADS + threadIdx.x;
+  if (v >= V) return;
+  const size_t C = (size_t)3 * V;
+  float p[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    float off = 0.f;
+#pragma unroll
+    for (int s = 0; s < SMPLX_PD_SPLIT; ++s) off += partial[s * C + 3 * v + k];
+    p[k] = off + v_shaped[3 * v + k];
+  }
+  float T[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) T[k] = 0.f;
+  const float* w = lbs_weights + (size_t)v * J;
+  for (int j = 0; j < J; ++j) {
+    const float wj = w[j];
+    if (wj != 0.f) {
+#pragma unroll
+      for (int k = 0; k < 12; ++k) T[k] += wj * s_A[12 * j + k];
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    const float o = T[r * 4 + 0] * p[0] + T[r * 4 + 1] * p[1] + T[r * 4 + 2] * p[2] + T[r * 4 + 3];
+    out_verts[3 * v + r] = o + (transl ? transl[r] : 0.f);
+  }
+}
+
+}  // namespace soar
+
+using namespace soar;
+
+extern "C" {
+
+size_t soar_smplx_workspace_bytes(int32_t V, int32_t J) {
+  return smplx_layout(V < 0 ? 0 : (size_t)V, J < 0 ? 0 : (size_t)J).total;
+}
+
+int soar_smplx_forward(const SoarSmplxModel* m, const float* betas, const float* full_pose,
+                       const float* transl, const float* inv_mats, float* out_verts,
+                       float* out_joints, float* out_A, float* out_bones, void* workspace,
+                       size_t workspace_bytes, soar_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!m) { set_error("soar_smplx_forward: model is NULL"); return SOAR_E_INVALID; }
+  const int V = m->V, J = m->J, NB = m->NB;
+  if (V <= 0 || J <= 0 || J > SMPLX_MAX_J || NB < 0 || NB > SMPLX_MAX_NB) {
+    set_error("soar_smplx_forward: bad sizes V=%d J=%d (<= %d) NB=%d (<= %d)", V, J, SMPLX_MAX_J, NB,
+              SMPLX_MAX_NB);
+    return SOAR_E_INVALID;
+  }
+  if (!m->v_template || !m->posedirs || !m->J_regressor || !m->parents || !m->lbs_weights ||
+      (NB > 0 && (!m->shapedirs || !betas)) || !full_pose) {
+    set_error("soar_smplx_forward: a required pointer is NULL");
+    return SOAR_E_INVALID;
+  }
+  if (out_bones && !inv_mats) {
+    set_error("soar_smplx_forward: out_bones needs inv_mats");
+    return SOAR_E_INVALID;
+  }
+  const SmplxLayout L = smplx_layout(V, J);
+  if (!workspace || workspace_bytes < L.total) {
+    set_error("soar_smplx_forward: workspace holds %zu bytes, need %zu", workspace_bytes, L.total);
+    return SOAR_E_WORKSPACE;
+  }
+  char* ws = reinterpret_cast<char*>(workspace);
+  float* v_shaped = reinterpret_cast<float*>(ws + L.v_shaped);
+  float* partial = reinterpret_cast<float*>(ws + L.partial);
+  float* joints = reinterpret_cast<float*>(ws + L.joints);
+  float* A_skin = reinterpret_cast<float*>(ws + L.A);
+  const int C = 3 * V;
+  const int n_feat = (J - 1) * 9;
+  const int rows = ceil_div(n_feat, SMPLX_PD_SPLIT);
+  {
+    KernelScope ks(K_SMPLX_SHAPE, stream);
+    smplx_shape_kernel<<<ceil_div(C, SMPLX_THREADS), SMPLX_THREADS, 0, stream>>>(
+        m->v_template, m->shapedirs, betas, C, NB, v_shaped);
+  }
+  SOAR_LAUNCH_CHECK("smplx_shape_kernel");
+  {
+    KernelScope ks(K_SMPLX_POSEDIRS, stream);
+    dim3 grid(ceil_div(C, SMPLX_THREADS), SMPLX_PD_SPLIT);
+    smplx_posedirs_kernel<<<grid, SMPLX_THREADS, (size_t)max(rows, 1) * sizeof(float), stream>>>(
+        m->posedirs, full_pose, C, n_feat, rows, partial);
+  }
+  SOAR_LAUNCH_CHECK("smplx_posedirs_kernel");
+  {
+    KernelScope ks(K_SMPLX_JOINTS, stream);
+    smplx_joints_kernel<<<J, SMPLX_THREADS, 0, stream>>>(m->J_regressor, v_shaped, V, joints);
+  }
+  SOAR_LAUNCH_CHECK("smplx_joints_kernel");
+  {
+    KernelScope ks(K_SMPLX_CHAIN, stream);
+    smplx_chain_kernel<<<1, SMPLX_MAX_J, 0, stream>>>(full_pose, m->parents, joints, transl, inv_mats,
+                                                      J, A_skin, out_joints, out_A, out_bones);
+  }
+  SOAR_LAUNCH_CHECK("smplx_chain_kernel");
+  if (out_verts) {
+    KernelScope ks(K_SMPLX_SKIN, stream);
+    smplx_skin_kernel<<<ceil_div(V, SMPLX_THREADS), SMPLX_THREADS, 0, stream>>>(
+        v_shaped, partial, m->lbs_weights, A_skin, transl, V, J, out_verts);
+  }
+  SOAR_LAUNCH_CHECK("smplx_skin_kernel");
+  return SOAR_OK;
+}
+
+}  // extern "C"

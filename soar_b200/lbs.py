@@ -80,3 +80,52 @@ def skin_gaussians(points, quats, weights, bones, swizzle=False):
         raise RuntimeError(f"skin_gaussians: weights {tuple(weights.shape)} do not match "
                            f"{points.shape[0]} points x {bones.shape[0]} bones")
     return _SkinGaussians.apply(points, quats, weights, bones, swizzle)
+
+
+class SkinWeightQuery:
+    """SMPL_Guidance.query_weights_smpl (TS/utils/smpl.py:618-637) on the sm_100a kernel
+    (soar_b200/csrc/lbs_query.cu): exact K nearest canonical vertices, distances clamped to
+    [1e-4, 1], inverse-distance blend of their skin-weight rows. The result is detached, like
+    the reference's (:611). `mats(points, bones)` fuses the bone blend of :613 and returns the
+    per-point 3x4 transforms without materialising the [N,J] weights."""
+
+    def __init__(self, cano_vertices, lbs_weights, K=30):
+        if not cano_vertices.is_cuda:
+            raise RuntimeError("SkinWeightQuery: CUDA tensors required (there is no CPU path)")
+        dev = cano_vertices.device
+        self.verts = cano_vertices.detach().to(device=dev, dtype=torch.float32).reshape(-1, 3).contiguous()
+        self.weights = lbs_weights.detach().to(device=dev, dtype=torch.float32)
+        if self.weights.dim() == 3:
+            self.weights = self.weights[0]
+        self.weights = self.weights.contiguous()
+        if self.weights.shape[0] != self.verts.shape[0]:
+            raise RuntimeError("SkinWeightQuery: lbs_weights must have one row per canonical vertex")
+        self.K = int(K)
+
+    def _run(self, points, bones, want_weights, want_mats):
+        if not points.is_cuda:
+            raise RuntimeError("SkinWeightQuery: points must be a CUDA tensor")
+        pts = points.detach().to(torch.float32).reshape(-1, 3).contiguous()
+        N, (V, J) = pts.shape[0], self.weights.shape
+        dev = pts.device
+        w = torch.empty((N, J), dtype=torch.float32, device=dev) if want_weights else None
+        m = torch.empty((N, 12), dtype=torch.float32, device=dev) if want_mats else None
+        b = None
+        if bones is not None:
+            b = bones.detach().to(device=dev, dtype=torch.float32).reshape(-1, 16).contiguous()
+            if b.shape[0] != J:
+                raise RuntimeError(f"SkinWeightQuery: {b.shape[0]} bones for {J} skin-weight columns")
+        with torch.cuda.device(dev):
+            _capi.check(_lib.soar_lbs_query_weights(_capi.ptr(pts), N, self.verts.data_ptr(), V,
+                                                    self.weights.data_ptr(), J, self.K, _capi.ptr(b),
+                                                    _capi.ptr(w), _capi.ptr(m), _stream()),
+                        "soar_lbs_query_weights")
+        return w, m
+
+    def __call__(self, points):
+        """points [N,3] -> skin weights [N,J]."""
+        return self._run(points, None, True, False)[0]
+
+    def mats(self, points, bones):
+        """points [N,3], bones [J,4,4] -> per-point transforms [N,12] (rows 0..2 of the blend)."""
+        return self._run(points, bones, False, True)[1]

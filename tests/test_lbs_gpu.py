@@ -55,3 +55,80 @@ def test_rigid_bones_give_rigid_motion():
     d_in = (pts[a] - pts[b]).norm(dim=1)
     d_out = (p[a] - p[b]).norm(dim=1)
     assert (d_in - d_out).abs().max().item() <= 1e-5
+
+
+# ---- SMPL-X forward (a17) and skin-weight query (a18) ----------------------------------------
+import glob as _glob
+import os as _os
+
+import numpy as _np
+
+_GOLDEN = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "golden")
+_SMPLX_CASES = sorted(_os.path.basename(p)[:-4] for p in _glob.glob(_os.path.join(_GOLDEN, "smplx_*.npz")))
+
+
+@pytest.mark.parametrize("name", _SMPLX_CASES)
+def test_smplx_forward_matches_reference_golden(name):
+    """soar_smplx_forward vs the outputs of the reference's own lbs() (float32; the kernels sum
+    in a different order than torch's matmuls: 3e-6 absolute on metres-scale outputs)."""
+    from soar_b200.smplx_fwd import SmplxPoser
+    d = _np.load(_os.path.join(_GOLDEN, name + ".npz"))
+    m = synthetic.smplx_template(V=int(d["V"]), NB=int(d["NB"]), seed=int(d["template_seed"]))
+    poser = SmplxPoser(*(m[k].cuda() for k in ("v_template", "shapedirs", "posedirs", "J_regressor",
+                                               "parents", "lbs_weights")))
+    t = lambda k: torch.from_numpy(d[k]).cuda()
+    verts, joints, A, bones = poser(t("betas"), t("full_pose"), t("transl"), t("inv_mats"))
+    for got, k in ((verts, "verts"), (joints, "joints"), (A, "A"), (bones, "bones")):
+        assert (got.cpu().numpy() - d[k]).reshape(-1).__abs__().max() <= 3e-6, k
+    # twice on the same workspace: deterministic (no float atomics)
+    v2, j2, A2, b2 = poser(t("betas"), t("full_pose"), t("transl"), t("inv_mats"))
+    assert torch.equal(verts, v2) and torch.equal(A, A2) and torch.equal(bones, b2)
+
+
+def test_smplx_forward_matches_oracle_other_pose():
+    from oracle import smplx_oracle
+    from soar_b200.smplx_fwd import SmplxPoser
+    m = synthetic.smplx_template(V=3000, NB=16, seed=9)
+    p = synthetic.smplx_pose(NB=16, seed=9, global_orient_zero=False)
+    o = smplx_oracle.smplx_forward({k: v.numpy() for k, v in m.items()}, p["betas"].numpy(),
+                                   p["full_pose"].numpy(), None)
+    poser = SmplxPoser(*(m[k].cuda() for k in ("v_template", "shapedirs", "posedirs", "J_regressor",
+                                               "parents", "lbs_weights")))
+    verts, joints, A, bones = poser(p["betas"].cuda(), p["full_pose"].cuda(), None, None)
+    assert bones is None
+    assert _np.abs(verts.cpu().numpy() - o["verts"]).max() <= 3e-6
+    assert _np.abs(joints.cpu().numpy() - o["joints"]).max() <= 3e-6
+    assert _np.abs(A.cpu().numpy() - o["A"]).max() <= 3e-6
+
+
+@pytest.mark.parametrize("N,V", [(1, 64), (1000, 500), (8_000, synthetic.N_VERTS)])
+def test_skin_weight_query_matches_oracle(N, V):
+    """Exact 30-NN + inverse-distance blend vs the torch restatement (cdist + topk). Weights are in
+    [0,1]: 2e-5 absolute (a neighbour swap at a distance tie only reorders equal contributions)."""
+    from soar_b200.lbs import SkinWeightQuery
+    m = synthetic.smplx_template(V=V, NB=1, seed=6)
+    gen = torch.Generator().manual_seed(N)
+    src = m["v_template"][torch.randint(0, V, (N,), generator=gen)]
+    pts = src + 0.02 * torch.randn(N, 3, generator=gen)
+    pts[: N // 4] = src[: N // 4]  # exactly on a vertex: distance clamps at 1e-4 (Q18)
+    want = lbs_oracle.query_weights(pts, m["v_template"], m["lbs_weights"], K=30)
+    q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda(), K=30)
+    got = q(pts.cuda())
+    assert got.shape == (N, synthetic.N_JOINTS)
+    assert (got.cpu() - want).abs().max().item() <= 2e-5
+    assert (got.sum(1) - 1).abs().max().item() <= 1e-5
+    # fused bone blend == weights @ bones
+    bones = synthetic.skinning_problem(8, seed=3)["bones"].cuda()
+    mats = q.mats(pts.cuda(), bones)
+    ref = (got @ bones.reshape(-1, 16))[:, :12]
+    assert (mats - ref).abs().max().item() <= 1e-5
+
+
+def test_skin_weight_query_rejects_cpu_and_bad_sizes():
+    from soar_b200.lbs import SkinWeightQuery
+    m = synthetic.smplx_template(V=64, NB=1, seed=6)
+    with pytest.raises(RuntimeError):
+        SkinWeightQuery(m["v_template"], m["lbs_weights"])
+    q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda(), K=64)
+    with pytest.raises(RuntimeError):
+        q(m["v_template"].cuda())
