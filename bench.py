@@ -55,6 +55,7 @@ def parse_args():
     ap.add_argument("--views-per-rank", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-lbs", action="store_true")
     return ap.parse_args()
 
 
@@ -380,6 +381,68 @@ def cpu_baseline(wl):
                 "sample": f"unavailable: {ex}"}
 
 
+def lbs_report(device, cpu=True, n=100_000):
+    """BASELINE config 1: SMPL-X LBS skinning of 100k canonical Gaussians to one pose. GPU: the
+    sm_100a kernels through the python API (SmplxPoser -> SkinWeightQuery -> skin_gaussians), CUDA
+    events. CPU: the reference's PyTorch op chain restated in oracle/lbs_oracle.py (the reference's
+    python cannot travel to this box), all host threads, synthetic 10475-vertex / 55-joint body."""
+    from soar_b200 import synthetic
+    from soar_b200.lbs import SkinWeightQuery, skin_gaussians
+    from soar_b200.smplx_fwd import SmplxPoser
+    m = synthetic.smplx_template()
+    pose = synthetic.smplx_pose()
+    gen = torch.Generator().manual_seed(7)
+    V = m["v_template"].shape[0]
+    pts = m["v_template"][torch.randint(0, V, (n,), generator=gen)] + 0.002 * torch.randn(n, 3, generator=gen)
+    quats = torch.nn.functional.normalize(torch.randn(n, 4, generator=gen), dim=1)
+    keys = ("v_template", "shapedirs", "posedirs", "J_regressor", "parents", "lbs_weights")
+    poser = SmplxPoser(*(m[k].to(device) for k in keys))
+    _, _, A0, _ = poser(pose["betas"].to(device), torch.zeros(165, device=device), None, None, want_verts=False)
+    inv = torch.linalg.inv(A0)
+    query = SkinWeightQuery(m["v_template"].to(device), m["lbs_weights"].to(device))
+    d = {k: v.to(device) for k, v in pose.items()}
+    pts_d, quats_d = pts.to(device), quats.to(device)
+
+    def gpu_stage():
+        _, _, _, bones = poser(d["betas"], d["full_pose"], d["transl"], inv, want_verts=False)
+        w = query(pts_d)
+        return skin_gaussians(pts_d, quats_d, w, bones, swizzle=True)
+
+    for _ in range(3):
+        out = gpu_stage()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 20
+    e0.record()
+    for _ in range(iters):
+        out = gpu_stage()
+    e1.record()
+    torch.cuda.synchronize()
+    rep = {"workload": f"c1: SMPL-X LBS of {n} canonical Gaussians to one pose (SMPL-X forward + 30-NN "
+                       "skin-weight query + bone blend + skinning of points and quaternions)",
+           "gpu_ms": e0.elapsed_time(e1) / iters}
+    if cpu:
+        try:
+            from oracle import lbs_oracle
+            inv_c = inv.cpu()
+            lbs_oracle.lbs_stage_cpu(m, pose, inv_c, pts, quats)  # warm-up
+            best = None
+            for _ in range(3):
+                t0 = time.perf_counter()
+                p_c, q_c, split = lbs_oracle.lbs_stage_cpu(m, pose, inv_c, pts, quats)
+                dt = (time.perf_counter() - t0) * 1e3
+                if best is None or dt < best[0]:
+                    best = (dt, split)
+            rep.update(cpu_ms=best[0], cpu_split=best[1], cpu_cores=torch.get_num_threads(),
+                       cpu_kind="port (oracle/lbs_oracle.py: torch restatement of the reference chain)",
+                       max_abs_points_gpu_vs_cpu=float((out[0].cpu() - p_c).abs().max()),
+                       speedup=best[0] / rep["gpu_ms"])
+        except Exception as ex:  # noqa: BLE001
+            rep["cpu_ms"] = None
+            rep["cpu_error"] = str(ex)
+    return rep
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -430,8 +493,18 @@ def main():
                 peak = float(json.load(f).get("hbm_gbs", peak))
             peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)"
         ach = alg.get(top, 0) / (t / cnt * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        if args.workload == "c3":  # measured DRAM bytes per launch from the committed ncu capture
+            import glob
+            tj = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
+            if tj:
+                with open(tj[-1]) as f:
+                    td = json.load(f)
+                traffic = td.get("bytes_per_launch", {}).get(top)
+                traffic_src = os.path.basename(tj[-1])
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                    "frac": ach / peak, "traffic": None, "avg_ms": t / cnt, "launches": cnt,
+                    "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "algorithmic_bytes": alg.get(top, 0), "avg_ms": t / cnt, "launches": cnt,
                     "peak_source": peak_src}
         shares = {k: {"launches": c, "ms": round(tt, 4), "share": round(tt / tot, 4),
                       "GBps": round(alg.get(k, 0) / (tt / c * 1e-3) / 1e9, 1) if tt > 0 else None}
@@ -443,6 +516,10 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.impl == "soar":
         cpu = cpu_baseline(wl)
+
+    lbs = None
+    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
+        lbs = lbs_report(device, cpu=not args.no_cpu_baseline)
 
     if rank == 0:
         line = {
@@ -457,7 +534,7 @@ def main():
                        "P_visible": Pv, "num_rendered": R,
                        "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,
-            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu,
+            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs,
         }
         if args.impl == "reference":
             line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",

@@ -87,3 +87,75 @@ def query_weights(points, cano_vertices, lbs_weights, K=30):
     ws = 1.0 / dist
     ws = ws / ws.sum(-1)[..., None]
     return (ws[..., None] * w).sum(-2)
+
+
+# ---- whole LBS stage on the host cores (bench.py's `lbs` baseline, BASELINE config 1) ---------
+def _rodrigues_t(rv):
+    """batch_rodrigues, TS/utils/smplx/lbs.py:293-328 (angle = |v + 1e-8|)."""
+    angle = torch.norm(rv + 1e-8, dim=1, keepdim=True)
+    d = rv / angle
+    c, s = torch.cos(angle)[:, None], torch.sin(angle)[:, None]
+    rx, ry, rz = d[:, 0:1], d[:, 1:2], d[:, 2:3]
+    z = torch.zeros_like(rx)
+    K = torch.cat([z, -rz, ry, rz, z, -rx, -ry, rx, z], dim=1).view(-1, 3, 3)
+    return torch.eye(3, dtype=rv.dtype)[None] + s * K + (1 - c) * torch.bmm(K, K)
+
+
+def smplx_forward_torch(model, betas, full_pose, transl):
+    """lbs() (TS/utils/smplx/lbs.py:147-246) + the transl fold (body_models.py:1380-1383) as the
+    same sequence of torch ops, batch 1, CPU. -> (verts [V,3], A [J,4,4])."""
+    J = model["J_regressor"].shape[0]
+    parents = model["parents"].tolist()
+    v_shaped = model["v_template"] + torch.einsum("bl,mkl->bmk", betas, model["shapedirs"])[0]
+    joints = torch.einsum("ik,ji->jk", v_shaped, model["J_regressor"])
+    R = _rodrigues_t(full_pose.view(-1, 3))
+    feat = (R[1:] - torch.eye(3)).reshape(1, -1)
+    v_posed = torch.matmul(feat, model["posedirs"]).view(-1, 3) + v_shaped
+    rel = joints.clone()
+    rel[1:] -= joints[parents[1:]]
+    T = torch.zeros(J, 4, 4)
+    T[:, :3, :3], T[:, :3, 3], T[:, 3, 3] = R, rel, 1.0
+    chain = [T[0]]
+    for i in range(1, J):
+        chain.append(torch.matmul(chain[parents[i]], T[i]))
+    G = torch.stack(chain)
+    A = G.clone()
+    A[:, :3, 3] -= torch.einsum("jab,jb->ja", G[:, :3, :3], joints)
+    Tv = torch.matmul(model["lbs_weights"], A.view(J, 16)).view(-1, 4, 4)
+    verts = torch.einsum("vab,vb->va", Tv[:, :3, :3], v_posed) + Tv[:, :3, 3]
+    t = transl.reshape(3)
+    A[:, :3, 3] += t
+    return verts + t, A
+
+
+def query_weights_chunked(points, cano_vertices, lbs_weights, K=30, chunk=8192):
+    """query_weights with the N x V distance matrix built 8192 rows at a time in float32 (the
+    reference goes through pytorch3d's float32 knn_points; a full float64 matrix at N = 100k
+    would need 8 GB)."""
+    outs = []
+    for s in range(0, points.shape[0], chunk):
+        p = points[s:s + chunk]
+        d2 = torch.cdist(p, cano_vertices).pow(2)
+        dist, idx = torch.topk(d2, K, dim=1, largest=False)
+        dist = dist.sqrt().clamp_(0.0001, 1.0)
+        ws = 1.0 / dist
+        ws = ws / ws.sum(-1)[..., None]
+        outs.append((ws[..., None] * lbs_weights[idx]).sum(-2))
+    return torch.cat(outs)
+
+
+def lbs_stage_cpu(model, pose, inv_mats, points, quats, swizzle=True):
+    """One LBS stage as the reference runs it per render (TS/utils/smpl.py:592-613 +
+    TS/renderer/diff_gaussian_rasterizer.py:103-114): SMPL-X forward, cano->live bones, skin-weight
+    query, bone blend, skinning of points and quaternions. Returns (points', quats', split_ms)."""
+    import time
+    t0 = time.perf_counter()
+    _, A = smplx_forward_torch(model, pose["betas"], pose["full_pose"], pose["transl"])
+    bones = torch.matmul(A, inv_mats)
+    t1 = time.perf_counter()
+    w = query_weights_chunked(points, model["v_template"], model["lbs_weights"])
+    t2 = time.perf_counter()
+    p, q, _ = skin(points, quats, w, bones, swizzle)
+    t3 = time.perf_counter()
+    return p, q, {"smplx_fwd_ms": (t1 - t0) * 1e3, "weight_query_ms": (t2 - t1) * 1e3,
+                  "blend_apply_ms": (t3 - t2) * 1e3}

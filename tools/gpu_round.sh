@@ -16,7 +16,7 @@ fi
 python bench.py --steps 20 --warmup 5 > $OUT/${TAG}_bench_soar.json 2> $OUT/${TAG}_bench_soar.err; echo "soar bench exit $?"
 cat $OUT/${TAG}_bench_reference.json $OUT/${TAG}_bench_soar.json
 if [ "${SKIP_NCU:-0}" != "1" ]; then
-SHORT="python bench.py --steps 1 --warmup 1 --views-per-rank 1 --no-e2e --no-cpu-baseline"
+SHORT="python bench.py --steps 1 --warmup 1 --views-per-rank 1 --no-e2e --no-cpu-baseline --no-lbs"
 $SHORT > $OUT/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu_launches.log 2>&1

@@ -48,6 +48,23 @@ def main():
         rows = list(csv.reader(raw.splitlines()))
         hdr, units, data = rows[0], rows[1], rows[2:]
         out.write(f"\n# full capture ({rp}): ncu --set full --clock-control none --import-source on\n")
+        # per-launch DRAM traffic of the largest launch of every kernel -> bench.py roofline.traffic
+        names = {"preprocess_fwd_kernel": "preprocess_fwd", "duplicate_tiles_kernel": "duplicate_keys",
+                 "radix_onesweep_kernel": "radix_onesweep", "blend_fwd_kernel": "blend_fwd",
+                 "blend_bwd_kernel": "blend_bwd", "geom_bwd_kernel": "geom_bwd"}
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        traffic = {}
+        for d in data:
+            kn = d[hdr.index("Kernel Name")]
+            for pat, short in names.items():
+                if pat in kn:
+                    b = float(d[ir].replace(",", "")) * scale[units[ir]] + float(d[iw].replace(",", "")) * scale[units[iw]]
+                    traffic[short] = max(traffic.get(short, 0.0), b)
+        import json
+        with open(os.path.join("profiles", f"{tag}_traffic.json"), "w") as tf:
+            json.dump({"source": f"ncu --set full capture {tag}_prof.ncu-rep (1 view of c3), dram__bytes_read.sum + "
+                                 "dram__bytes_write.sum per launch", "bytes_per_launch": traffic}, tf, indent=1)
         for d in data:
             out.write(f"\n## {d[hdr.index('Kernel Name')][:100]}\n")
             for m in METRICS:
