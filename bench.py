@@ -427,7 +427,7 @@ def lbs_report(device, cpu=True, n=100_000):
             inv_c = inv.cpu()
             lbs_oracle.lbs_stage_cpu(m, pose, inv_c, pts, quats)  # warm-up
             best = None
-            for _ in range(3):
+            for _ in range(2):
                 t0 = time.perf_counter()
                 p_c, q_c, split = lbs_oracle.lbs_stage_cpu(m, pose, inv_c, pts, quats)
                 dt = (time.perf_counter() - t0) * 1e3

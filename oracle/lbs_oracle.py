@@ -135,7 +135,9 @@ def query_weights_chunked(points, cano_vertices, lbs_weights, K=30, chunk=8192):
     outs = []
     for s in range(0, points.shape[0], chunk):
         p = points[s:s + chunk]
-        d2 = torch.cdist(p, cano_vertices).pow(2)
+        # direct differences like pytorch3d's knn_points (the |a|^2+|b|^2-2ab shortcut loses the
+        # millimetre-scale distances to cancellation in float32)
+        d2 = torch.cdist(p, cano_vertices, compute_mode="donot_use_mm_for_euclid_dist").pow(2)
         dist, idx = torch.topk(d2, K, dim=1, largest=False)
         dist = dist.sqrt().clamp_(0.0001, 1.0)
         ws = 1.0 / dist

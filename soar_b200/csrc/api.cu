@@ -287,7 +287,8 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
     }
   }
   GeomBwdArgs g;
-  g.P = v->P; g.D = v->sh_degree; g.M = v->M;
+  g.P = v->P; g.D = v->sh_degree; g.M = v->M; g.W = v->width; g.H = v->height;
+  g.records = v->P > 0 ? reinterpret_cast<const float*>(at(geom, GL.records)) : nullptr;
   g.tanfovx = v->tanfovx; g.tanfovy = v->tanfovy;
   g.focal_y = v->height / (2.0f * v->tanfovy);
   g.focal_x = v->width / (2.0f * v->tanfovx);

@@ -7,10 +7,11 @@
 //
 // What is ours:
 //   * the reference issues 13 global atomicAdds per (pixel, Gaussian) contribution. Here
-//     the 13 values are reduced across the 32 pixels of a warp with a transposed butterfly
-//     (16 shuffles for all 13 values together, not 5 per value), the 8 warps of the tile
-//     meet in a shared-memory accumulator, and the tile flushes ONE set of vectorised
-//     global reductions per Gaussian per batch into a 64-byte per-Gaussian accumulator;
+//     the partials are reduced across the 32 pixels of a warp with a transposed butterfly
+//     (12 or 16 shuffles for all 10 / 14 values together, not 5 per value) and the warp adds
+//     its totals with ONE warp-wide reduction instruction into the Gaussian's 64-byte
+//     accumulator line (10 / 14 consecutive words); the mean2D / conic gradients are formed
+//     from moment sums once per Gaussian in geom_bwd.cu, not per contribution;
 //   * the replay starts at the tile's deepest n_contrib instead of the end of its range;
 //   * list entries that cannot reach alpha >= 1/255 anywhere in the tile are dropped at
 //     staging time, and every warp (an 8x4 pixel block) only visits the entries whose
@@ -36,12 +37,6 @@ __device__ __forceinline__ float rcp_approx(float x) {
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
-}
-
-__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c),
-               "f"(d)
-               : "memory");
 }
 
 // Sum v[0..15] over the 32 lanes; on return lane l holds the total of value
@@ -84,14 +79,14 @@ __device__ __forceinline__ float warp_reduce16(float (&v)[16], uint32_t lane) {
   return v[0];
 }
 
-// In-kernel slot order of the per-(pixel, Gaussian) partials. The six dL/ddist moments
-// (sum of dd, dd*dx, dd*dy, dd*dx^2, dd*dx*dy, dd*dy^2 with d = centre - pixel) replace the
-// reference's five mean2D/conic sums: they are cheaper to form per pixel and are turned into
-// dL/dmean2D and dL/dconic once per (tile, Gaussian) at flush time. Variants without surface
-// normals only carry the first 10 slots (12-shuffle reduction instead of 16).
+// Slot order of the per-(pixel, Gaussian) partials = the accumulator's (layout.h, GaccSlot). The
+// six dL/ddist moments replace the reference's five mean2D/conic sums: they are cheaper to form
+// per pixel and need no per-tile conversion. Variants without surface normals only carry the
+// first 10 slots (12-shuffle reduction instead of 16).
 enum LocalSlot {
-  LS_DC0 = 0, LS_DC1 = 1, LS_DC2 = 2, LS_DD = 3, LS_DO = 4, LS_MX = 5, LS_MY = 6, LS_MXX = 7,
-  LS_MXY = 8, LS_MYY = 9, LS_DN0 = 10, LS_DN1 = 11, LS_DN2 = 12, LS_GD = 13, LS_COUNT = 14
+  LS_DC0 = GA_DC0, LS_DC1 = GA_DC1, LS_DC2 = GA_DC2, LS_DD = GA_DD, LS_DO = GA_DO, LS_MX = GA_MX,
+  LS_MY = GA_MY, LS_MXX = GA_MXX, LS_MXY = GA_MXY, LS_MYY = GA_MYY, LS_DN0 = GA_DN0,
+  LS_DN1 = GA_DN1, LS_DN2 = GA_DN2, LS_GD = GA_GD, LS_COUNT = GA_COUNT
 };
 
 // Sum v[0..9] over the 32 lanes with 12 shuffles. Returns the total of slot `idx` (output);
@@ -143,7 +138,6 @@ struct BlendBwdSmem {
   uint32_t id[BWD_BATCH];
   uint32_t pos[BWD_BATCH];  // 0-based position in the tile's list
   uint8_t mask[BWD_BATCH];
-  float acc[BWD_BATCH][GACC_FLOATS];
   uint32_t wcount[N_BLK];
   uint32_t max_contrib[N_BLK];
 };
@@ -175,8 +169,6 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   for (int o = 16; o > 0; o >>= 1)
     block_depth = max(block_depth, __shfl_xor_sync(0xffffffffu, block_depth, o));
   if (lane == 0) sm.max_contrib[warp] = block_depth;
-#pragma unroll
-  for (int k = 0; k < GACC_FLOATS; ++k) sm.acc[tid][k] = 0.f;
   __syncthreads();
   uint32_t tile_depth = 0;
 #pragma unroll
@@ -215,8 +207,6 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
 
   float T = T_final;
   float S = 0.f, cg_last = 0.f, last_alpha = 0.f;
-  const float ddelx_dx = 0.5 * a.W;
-  const float ddely_dy = 0.5 * a.H;
 
   for (int i = 0; i < rounds; i++) {
     // ---- stage (from the back), cull against the tile, compact in walk order ---------
@@ -339,55 +329,27 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           v[LS_MYY] = ddy * d.y;
         }
 
+        // one warp-wide RED: the lanes holding a total hit consecutive words of the Gaussian's
+        // 64-byte accumulator line (native fp32 reduction at L2; shared-memory float atomics are
+        // compare-and-swap loops)
+        float* const g = a.gacc + (size_t)sm.id[j] * GACC_FLOATS;
         if (SURFACE) {
           const float total = warp_reduce16(v, lane);
-          if ((lane & 1) == 0 && (lane >> 1) < LS_COUNT) atomicAdd(&sm.acc[j][lane >> 1], total);
+          if ((lane & 1) == 0 && (lane >> 1) < LS_COUNT) atomicAdd(g + (lane >> 1), total);
         } else {
           int slot_idx;
           const float total = warp_reduce10(v, lane, slot_idx);
-          if (slot_idx >= 0) atomicAdd(&sm.acc[j][slot_idx], total);
+          if (slot_idx >= 0) atomicAdd(g + slot_idx, total);
         }
       }
     }
-    __syncthreads();
-
-    // flush this batch: thread t owns compacted entry t and turns its moment sums into the
-    // reference's 13 per-Gaussian partials (backward.cu:820-855)
-    if ((uint32_t)tid < n) {
-      float* acc = sm.acc[tid];
-      bool any = false;
-#pragma unroll
-      for (int k = 0; k < LS_COUNT; ++k) any = any || (acc[k] != 0.f);
-      if (any) {
-        const float4 e0 = sm.q0[tid], e1 = sm.q1[tid];
-        const float cA = e0.z, cB = e0.w, cC = e1.x;
-        const float mx = acc[LS_MX], my = acc[LS_MY];
-        float ndc_x = 2 * (cA * mx + cB * my) * ddelx_dx;
-        float ndc_y = 2 * (cC * my + cB * mx) * ddely_dy;
-        if (DEPTH_DIFF) {
-          const float4 e4 = sm.q4[tid];
-          const float J6 = sm.q2[tid].w, J9 = sm.q3[tid].w;
-          ndc_x += -acc[LS_GD] * (J6 * e4.x + J9 * e4.z);
-          ndc_y += -acc[LS_GD] * (J6 * e4.y + J9 * e4.w);
-        }
-        float* g = a.gacc + (size_t)sm.id[tid] * GACC_FLOATS;
-        // GA_* order: dcolor[3] dnormal[3] ddepth dmean2D.xy dconic.(a,b,c) dopacity
-        red_add_v4(g + 0, acc[LS_DC0], acc[LS_DC1], acc[LS_DC2], SURFACE ? acc[LS_DN0] : 0.f);
-        red_add_v4(g + 4, SURFACE ? acc[LS_DN1] : 0.f, SURFACE ? acc[LS_DN2] : 0.f, acc[LS_DD], ndc_x);
-        red_add_v4(g + 8, ndc_y, acc[LS_MXX], acc[LS_MXY], acc[LS_MYY]);
-        atomicAdd(g + 12, acc[LS_DO]);
-#pragma unroll
-        for (int k = 0; k < LS_COUNT; ++k) acc[k] = 0.f;
-      }
-    }
-    // the next round's staging writes happen after its first barrier; the flush above only
-    // touches rows < n of this round, which the next round's atomics reach after that barrier
+    // no barrier here: the next round only overwrites the batch after its own first barrier
   }
 }
 
 // The config flags live in device memory (backward.cu:581): one kernel, specialised bodies
 // selected by a uniform branch.
-__global__ void __launch_bounds__(TILE_PIX, 3) blend_bwd_kernel(const BlendBwdArgs a) {
+__global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdArgs a) {
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;

@@ -71,14 +71,30 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
 
   if (visible) {
     const bool surface = a.config[0] > 0;
+    // accumulator (layout.h GaccSlot): dcolor[3] ddepth dopacity | six dL/ddist moments |
+    // dnormal[3] and the per-pixel-depth sum
     const float4* acc4 = reinterpret_cast<const float4*>(a.gacc + (size_t)idx * GACC_FLOATS);
     const float4 A0 = acc4[0], A1 = acc4[1], A2 = acc4[2], A3 = acc4[3];
     const float dL_dcolor[3] = {A0.x, A0.y, A0.z};
-    const float dL_dnormal[3] = {A0.w, A1.x, A1.y};
-    const float dL_ddepth = A1.z;
-    const float2 dL_dmean2d = {A1.w, A2.x};
-    const float3 dL_dconic = {A2.y, A2.z, A2.w};
-    const float dL_dopac = A3.x;
+    const float dL_ddepth = A0.w;
+    const float dL_dopac = A1.x;
+    const float m_x = A1.y, m_y = A1.z, m_xx = A1.w, m_xy = A2.x, m_yy = A2.y;
+    const float dL_dnormal[3] = {A2.z, A2.w, A3.x};
+    // dL/dmean2D (NDC-scaled, Q10) and dL/dconic from the moments (backward.cu:820-855), with the
+    // conic the blend kernels used (the forward's record)
+    const float4* rec = reinterpret_cast<const float4*>(a.records + (size_t)idx * REC_FLOATS);
+    const float4 r0 = __ldg(rec + 0), r1 = __ldg(rec + 1);
+    const float cA = r0.z, cB = r0.w, cC = r1.x;
+    const float ddelx_dx = 0.5 * a.W;
+    const float ddely_dy = 0.5 * a.H;
+    float2 dL_dmean2d = {2 * (cA * m_x + cB * m_y) * ddelx_dx, 2 * (cC * m_y + cB * m_x) * ddely_dy};
+    if (surface && a.config[2] > 0) {
+      const float4 r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4);
+      const float J6 = r2.w, J9 = r3.w, gd = A3.y;
+      dL_dmean2d.x += -gd * (J6 * r4.x + J9 * r4.z);
+      dL_dmean2d.y += -gd * (J6 * r4.y + J9 * r4.w);
+    }
+    const float3 dL_dconic = {m_xx, m_xy, m_yy};
 
     {
       float* p = a.g.dL_dmeans2D + 3 * (size_t)idx;

@@ -83,7 +83,8 @@ struct BlendBwdArgs {
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream);
 
 struct GeomBwdArgs {
-  int P, D, M;
+  int P, D, M, W, H;
+  const float* records;  // the forward's per-Gaussian records (conic, Jinv)
   float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
   const float* means3D;
   const int* radii;

@@ -130,11 +130,14 @@ inline BinningLayout binning_layout(size_t R, int passes) {
 }
 
 // ---- backward scratch: per-Gaussian accumulator written by the blend backward ----
-// 16 floats: dcolor[3] dnormal[3] ddepth dmean2D.xy dconic.(a,b,c) dopacity pad[3]
+// 16 floats. The blend backward adds, per (warp, Gaussian) visit, the warp's sums of the
+// colour / depth / opacity partials and of the six dL/ddist moments (sum of dd, dd*dx, dd*dy,
+// dd*dx^2, dd*dx*dy, dd*dy^2 with d = centre - pixel); the per-Gaussian geometry backward turns
+// the moments into dL/dmean2D and dL/dconic (backward.cu:820-855) once per Gaussian.
 constexpr int GACC_FLOATS = 16;
 enum GaccSlot {
-  GA_DC0 = 0, GA_DC1 = 1, GA_DC2 = 2, GA_DN0 = 3, GA_DN1 = 4, GA_DN2 = 5, GA_DD = 6,
-  GA_DMX = 7, GA_DMY = 8, GA_DCA = 9, GA_DCB = 10, GA_DCC = 11, GA_DO = 12
+  GA_DC0 = 0, GA_DC1 = 1, GA_DC2 = 2, GA_DD = 3, GA_DO = 4, GA_MX = 5, GA_MY = 6, GA_MXX = 7,
+  GA_MXY = 8, GA_MYY = 9, GA_DN0 = 10, GA_DN1 = 11, GA_DN2 = 12, GA_GD = 13, GA_COUNT = 14
 };
 
 }  // namespace soar
