@@ -56,6 +56,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-lbs", action="store_true")
+    ap.add_argument("--sequential", action="store_true",
+                    help="one blocking forward+backward per view through autograd's own gradient "
+                         "accumulation (no begin-all pipelining, no in-place accumulation)")
     return ap.parse_args()
 
 
@@ -124,6 +127,7 @@ class Workload:
         self.name = name
         self.P, self.W, self.H, self.deg = WORKLOADS[name]
         self.device, self.rank, self.world, self.vpr = device, rank, world, views_per_rank
+        self.pipelined = True
         g = synthetic.gaussians(self.P, sh_degree=self.deg, seed=0)
         self.params = {k: g[k].to(device).requires_grad_(True) for k in PARAM_KEYS if g.get(k) is not None}
         self.flat = FlatGrads(self.params)
@@ -154,6 +158,8 @@ class Workload:
         self.copy_stream = torch.cuda.Stream(device=device)
         self.copied = [torch.cuda.Event() for _ in range(2)]
         self.consumed = [torch.cuda.Event() for _ in range(2)]
+        self.cam_all = [torch.empty(35, **f32) for _ in range(views_per_rank)]
+        self.cams_copied, self.cams_consumed = torch.cuda.Event(), torch.cuda.Event()
         self.loss_host = torch.zeros(1).pin_memory()
 
     def scene_dict(self, cam_flat):
@@ -197,6 +203,31 @@ class SoarArm:
         return self.R(st)(means3D=p["means3D"], means2D=means2D, opacities=p["opacities"],
                           shs=p.get("shs"), colors_precomp=p.get("colors_precomp"),
                           scales=p["scales"], rotations=p["rotations"])
+
+    def _rasterizer(self, cam_flat):
+        wl = self.wl
+        st = self.S(image_height=wl.H, image_width=wl.W, tanfovx=wl.tanfovx, tanfovy=wl.tanfovy,
+                    bg=wl.bg, scale_modifier=1.0, viewmatrix=cam_flat[0:16].view(4, 4),
+                    projmatrix=cam_flat[16:32].view(4, 4), patch_bbox=wl.patch_bbox,
+                    prcppoint=wl.prcppoint, sh_degree=wl.deg, campos=cam_flat[32:35],
+                    prefiltered=False, render_front=False, sort_descending=False, debug=False,
+                    config=wl.config)
+        p = wl.params
+        kw = dict(means3D=p["means3D"], means2D=torch.zeros_like(p["means3D"], requires_grad=True),
+                  opacities=p["opacities"], shs=p.get("shs"), colors_precomp=p.get("colors_precomp"),
+                  scales=p["scales"], rotations=p["rotations"])
+        return self.R(st), kw
+
+    def views_resident(self, cams):
+        """All views of a step: phase 1 of every view enqueued up front (views.iter_views),
+        gradients accumulated in place in the flat buffer (FlatGrads.direct)."""
+        from soar_b200.views import iter_views
+        c = self.wl.cot
+        rs, kws = zip(*(self._rasterizer(cam) for cam in cams))
+        with self.wl.flat.direct():
+            for color, normal, depth, opac, _ in iter_views(rs, kws):
+                torch.autograd.backward([color, normal, depth, opac],
+                                        [c["color"], c["normal"], c["depth"], c["opac"]])
 
     def view_resident(self, cam_flat):
         color, normal, depth, opac, _ = self._render(cam_flat)
@@ -264,8 +295,11 @@ def max_over_ranks(ms, world, device):
 
 def step_resident(arm, wl, step):
     wl.flat.zero_()
-    for v in range(wl.vpr):
-        arm.view_resident(wl.cam_dev[wl.view_index(step, v)])
+    if wl.pipelined and hasattr(arm, "views_resident"):
+        arm.views_resident([wl.cam_dev[wl.view_index(step, v)] for v in range(wl.vpr)])
+    else:
+        for v in range(wl.vpr):
+            arm.view_resident(wl.cam_dev[wl.view_index(step, v)])
     wl.flat.allreduce()
 
 
@@ -279,7 +313,52 @@ def _stage_view(wl, step, v, slot):
         wl.copied[slot].record(wl.copy_stream)
 
 
+def step_e2e_pipelined(arm, wl, step):
+    """The e2e step on the product's multi-view path: this step's cameras are copied first (35
+    floats each) so phase 1 of every view can be enqueued up front; target images stay double
+    buffered on the copy stream; gradients accumulate in place in the flat buffer."""
+    from soar_b200.views import iter_views
+    wl.flat.zero_()
+    main = torch.cuda.current_stream()
+    with torch.cuda.stream(wl.copy_stream):
+        wl.copy_stream.wait_event(wl.cams_consumed)
+        for v in range(wl.vpr):
+            wl.cam_all[v].copy_(wl.cam_host[wl.view_index(step, v)], non_blocking=True)
+        wl.cams_copied.record(wl.copy_stream)
+
+    def stage_target(v, slot):
+        with torch.cuda.stream(wl.copy_stream):
+            wl.copy_stream.wait_event(wl.consumed[slot])
+            i = wl.view_index(step, v)
+            wl.tgt_dev[slot].copy_(wl.tgt_host[i % len(wl.tgt_host)], non_blocking=True)
+            wl.copied[slot].record(wl.copy_stream)
+
+    stage_target(0, 0)
+    main.wait_event(wl.cams_copied)
+    rs, kws = zip(*(arm._rasterizer(wl.cam_all[v]) for v in range(wl.vpr)))
+    total = None
+    with wl.flat.direct():
+        for v, (color, normal, depth, opac, _) in enumerate(iter_views(rs, kws)):
+            slot = v & 1
+            if v + 1 < wl.vpr:
+                stage_target(v + 1, slot ^ 1)
+            main.wait_event(wl.copied[slot])
+            tgt = wl.tgt_dev[slot]
+            loss = (((color - tgt[0:3]) ** 2).mean() + ((normal - tgt[3:6]) ** 2).mean()
+                    + ((depth - tgt[6:7]) ** 2).mean() + ((opac - tgt[7:8]) ** 2).mean())
+            loss.backward()
+            wl.consumed[slot].record(main)
+            total = loss.detach() if total is None else total + loss.detach()
+    wl.cams_consumed.record(main)
+    wl.flat.allreduce()
+    wl.loss_host.copy_(total.reshape(1), non_blocking=True)
+    torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
+    return float(wl.loss_host[0])
+
+
 def step_e2e(arm, wl, step):
+    if wl.pipelined and hasattr(arm, "views_resident"):
+        return step_e2e_pipelined(arm, wl, step)
     wl.flat.zero_()
     total = None
     main = torch.cuda.current_stream()
@@ -457,6 +536,7 @@ def main():
     device = torch.device("cuda", local)
 
     wl = Workload(args.workload, device, rank, world, args.views_per_rank)
+    wl.pipelined = not args.sequential
     arm = SoarArm(wl) if args.impl == "soar" else ReferenceArm(wl)
     Pv, R = scene_stats(wl)
     from soar_b200 import _capi
@@ -531,6 +611,10 @@ def main():
                                    f"{wl.P} Gaussians, SH degree {wl.deg}",
                        "views_per_rank_per_step": wl.vpr, "global_views_per_step": wl.vpr * world,
                        "parallelism": f"view-sharded x{world}, 1 allreduce of {wl.flat.nbytes()} B/step" if world > 1 else "single GPU",
+                       "view_loop": ("phase 1 of all views of a step enqueued up front "
+                                     "(soar_b200.views.iter_views) + in-place gradient accumulation "
+                                     "(FlatGrads.direct)") if (wl.pipelined and args.impl == "soar")
+                       else "one blocking forward+backward per view, autograd gradient accumulation",
                        "P_visible": Pv, "num_rendered": R,
                        "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,

@@ -51,23 +51,41 @@ def _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered, r
     return v
 
 
-def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
-                        cov3D_precomp, viewmatrix, projmatrix, prcppoint, patchbbox, tan_fovx,
-                        tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
-                        render_front, sort_descending, debug, config):
-    """Forward. Returns (num_rendered, color[3,H,W], normal[3,H,W], depth[1,H,W],
-    opac[1,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer) like
-    RasterizeGaussiansCUDA (DGR/rasterize_points.cu:35-105)."""
+class _PinnedStatus:
+    """Pool of page-locked 2-word host buffers for the asynchronous num_rendered read-back."""
+    _free = []
+
+    @classmethod
+    def get(cls):
+        return cls._free.pop() if cls._free else torch.zeros(2, dtype=torch.int32).pin_memory()
+
+    @classmethod
+    def put(cls, t):
+        cls._free.append(t)
+
+
+class PendingRaster:
+    """Phase 1 of a forward (preprocess, depth order, scan) enqueued, count not yet read."""
+    __slots__ = ("view", "keep", "P", "H", "W", "dev", "radii", "geom", "status", "event", "debug")
+
+
+def rasterize_gaussians_begin(background, means3D, colors, opacity, scales, rotations,
+                              scale_modifier, cov3D_precomp, viewmatrix, projmatrix, prcppoint,
+                              patchbbox, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                              campos, prefiltered, render_front, sort_descending, debug, config):
+    """Enqueue phase 1 of the forward on the current stream WITHOUT waiting for num_rendered
+    (soar_rast_forward_bin_async). A multi-view step calls this for all its views, then
+    rasterize_gaussians_finish() for each: the host wait of view k overlaps the device work of
+    the views behind it. Same arguments as rasterize_gaussians."""
     if means3D.dim() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    pend = PendingRaster()
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     dev = means3D.device
-    byte = dict(dtype=torch.uint8, device=dev)
+    pend.P, pend.H, pend.W, pend.dev, pend.debug = P, H, W, dev, bool(debug)
+    pend.view = pend.keep = pend.radii = pend.geom = pend.status = pend.event = None
     if P == 0:
-        z = lambda c: torch.zeros((c, H, W), dtype=torch.float32, device=dev)
-        e = torch.empty(0, **byte)
-        return (0, z(3), z(3), z(1), z(1), torch.zeros(0, dtype=torch.int32, device=dev), e,
-                e.clone(), e.clone())
+        return pend
 
     means3D = _f32(means3D, "means3D")
     sh, colors = _f32(sh, "sh"), _f32(colors, "colors_precomp")
@@ -79,55 +97,115 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     M = sh.size(1) if sh is not None else 0
 
     with torch.cuda.device(dev):
-        view = _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered,
-                     render_front, sort_descending, debug, background, means3D, sh, colors, opacity,
-                     scales, rotations, cov3D_precomp, viewmatrix, projmatrix, prcppoint, patchbbox,
-                     campos, config)
-        stream = _stream()
-        radii = torch.empty(P, dtype=torch.int32, device=dev)
-        geom = torch.empty(_lib.soar_rast_geom_bytes(P), **byte)
-        img = torch.empty(_lib.soar_rast_image_bytes(W, H), **byte)
-        rendered = ctypes.c_uint32(0)
-        _capi.check(_lib.soar_rast_forward_bin(ctypes.byref(view), geom.data_ptr(), geom.numel(),
-                                               radii.data_ptr(), ctypes.byref(rendered), stream),
+        pend.view = _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered,
+                          render_front, sort_descending, debug, background, means3D, sh, colors,
+                          opacity, scales, rotations, cov3D_precomp, viewmatrix, projmatrix,
+                          prcppoint, patchbbox, campos, config)
+        # the view struct holds raw pointers: keep the (possibly converted) tensors alive
+        pend.keep = (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
+                     viewmatrix, projmatrix, prcppoint, patchbbox, campos, config)
+        pend.radii = torch.empty(P, dtype=torch.int32, device=dev)
+        pend.geom = torch.empty(_lib.soar_rast_geom_bytes(P), dtype=torch.uint8, device=dev)
+        pend.status = _PinnedStatus.get()
+        _capi.check(_lib.soar_rast_forward_bin_async(ctypes.byref(pend.view), pend.geom.data_ptr(),
+                                                     pend.geom.numel(), pend.radii.data_ptr(),
+                                                     pend.status.data_ptr(), _stream()),
                     "rasterize_gaussians (preprocess)")
-        R = int(rendered.value)
+        pend.event = torch.cuda.Event()
+        pend.event.record(torch.cuda.current_stream())
+    return pend
+
+
+def rasterize_gaussians_finish(pend):
+    """Wait for the count of a begun forward, size the binning buffer, enqueue phase 2 on the
+    current stream (must be the stream phase 1 was enqueued on). Returns the 9-tuple of
+    rasterize_gaussians."""
+    P, H, W, dev = pend.P, pend.H, pend.W, pend.dev
+    byte = dict(dtype=torch.uint8, device=dev)
+    if P == 0:
+        z = lambda c: torch.zeros((c, H, W), dtype=torch.float32, device=dev)
+        e = torch.empty(0, **byte)
+        return (0, z(3), z(3), z(1), z(1), torch.zeros(0, dtype=torch.int32, device=dev), e,
+                e.clone(), e.clone())
+    pend.event.synchronize()  # the one host wait of the forward (reference: rasterizer_impl.cu:250)
+    R, flag = int(pend.status[0]) & 0xffffffff, int(pend.status[1])
+    _PinnedStatus.put(pend.status)
+    pend.status = None
+    if flag:
+        raise RuntimeError("rasterize_gaussians (preprocess) failed: Point is filtered although "
+                           "prefiltered is set. This shouldn't happen!")
+    with torch.cuda.device(dev):
+        stream = _stream()
+        img = torch.empty(_lib.soar_rast_image_bytes(W, H), **byte)
         binning = torch.empty(_lib.soar_rast_binning_bytes(R, W, H), **byte)
         f32 = dict(dtype=torch.float32, device=dev)
         color = torch.empty((3, H, W), **f32)
         normal = torch.empty((3, H, W), **f32)
         depth = torch.empty((1, H, W), **f32)
         opac = torch.empty((1, H, W), **f32)
-        _capi.check(_lib.soar_rast_forward_render(ctypes.byref(view), geom.data_ptr(),
+        _capi.check(_lib.soar_rast_forward_render(ctypes.byref(pend.view), pend.geom.data_ptr(),
                                                   binning.data_ptr(), binning.numel(),
                                                   img.data_ptr(), img.numel(), R, color.data_ptr(),
                                                   normal.data_ptr(), depth.data_ptr(),
                                                   opac.data_ptr(), stream),
                     "rasterize_gaussians (render)")
-        if debug:
+        if pend.debug:
             torch.cuda.synchronize(dev)  # reference: CHECK_CUDA syncs after every launch
+    radii, geom = pend.radii, pend.geom
+    pend.view = pend.keep = None
     return R, color, normal, depth, opac, radii, geom, binning, img
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, viewmatrix, projmatrix, prcppoint, patchbbox, tan_fovx,
+                        tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                        render_front, sort_descending, debug, config):
+    """Forward. Returns (num_rendered, color[3,H,W], normal[3,H,W], depth[1,H,W],
+    opac[1,H,W], radii[P] int32, geomBuffer, binningBuffer, imgBuffer) like
+    RasterizeGaussiansCUDA (DGR/rasterize_points.cu:35-105)."""
+    return rasterize_gaussians_finish(rasterize_gaussians_begin(
+        background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+        viewmatrix, projmatrix, prcppoint, patchbbox, tan_fovx, tan_fovy, image_height, image_width,
+        sh, degree, campos, prefiltered, render_front, sort_descending, debug, config))
 
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations,
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, prcppoint,
                                  patchbbox, tan_fovx, tan_fovy, dL_dout_color, dL_dout_normal,
                                  dL_dout_depth, dL_dout_opac, sh, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug, config):
+                                 binningBuffer, imageBuffer, debug, config, accumulate=None):
     """Backward. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations, dL_dviewmat, dL_dprojmat, dL_dcampos) like
-    RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187)."""
+    RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187).
+
+    Extension: `accumulate` maps any of "means3D", "colors", "opacity", "sh", "scales",
+    "rotations", "cov3D" to a caller-owned float32 buffer of the gradient's shape; this view's
+    gradient is then ADDED to it in place (SoarRastGrads.accumulate_mask) and the buffer itself
+    is returned in the tuple."""
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     dev = means3D.device
     f32 = dict(dtype=torch.float32, device=dev)
     sh = _f32(sh, "sh")
     M = sh.size(1) if sh is not None else 0
-    alloc = torch.empty if P > 0 else torch.zeros
-    g_means3D, g_means2D = alloc((P, 3), **f32), alloc((P, 3), **f32)
-    g_colors, g_opacity = alloc((P, 3), **f32), alloc((P, 1), **f32)
-    g_cov3D, g_sh = alloc((P, 6), **f32), alloc((P, M, 3), **f32)
-    g_scales, g_rot = alloc((P, 3), **f32), alloc((P, 4), **f32)
+    acc = accumulate or {}
+    mask = 0
+
+    def alloc(shape, name=None, bit=0):
+        nonlocal mask
+        buf = acc.get(name) if name else None
+        if buf is not None and P > 0:
+            if buf.dtype != torch.float32 or not buf.is_contiguous() or buf.numel() != P * (
+                    shape[1] if len(shape) == 2 else shape[1] * shape[2]):
+                raise RuntimeError(f"accumulate[{name!r}] must be a contiguous float32 buffer of shape {shape}")
+            mask |= bit
+            return buf
+        return (torch.empty if P > 0 else torch.zeros)(shape, **f32)
+
+    g_means3D, g_means2D = alloc((P, 3), "means3D", _capi.ACC_MEANS3D), alloc((P, 3))
+    g_colors, g_opacity = alloc((P, 3), "colors", _capi.ACC_COLORS), alloc((P, 1), "opacity", _capi.ACC_OPACITY)
+    g_cov3D, g_sh = alloc((P, 6), "cov3D", _capi.ACC_COV3D), alloc((P, M, 3), "sh" if M else None, _capi.ACC_SH)
+    g_scales, g_rot = alloc((P, 3), "scales", _capi.ACC_SCALES), alloc((P, 4), "rotations", _capi.ACC_ROTATIONS)
     g_view, g_proj, g_campos = torch.zeros((4, 4), **f32), torch.zeros((4, 4), **f32), torch.zeros(3, **f32)
     if P == 0:
         return (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot, g_view,
@@ -155,6 +233,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         grads.dL_dscales, grads.dL_drotations = g_scales.data_ptr(), g_rot.data_ptr()
         grads.dL_dviewmat, grads.dL_dprojmat = g_view.data_ptr(), g_proj.data_ptr()
         grads.dL_dcampos = g_campos.data_ptr()
+        grads.accumulate_mask = mask
         scratch = torch.empty(_lib.soar_rast_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
         _capi.check(_lib.soar_rast_backward(ctypes.byref(view), radii.data_ptr(),
                                             geomBuffer.data_ptr(), binningBuffer.data_ptr(),

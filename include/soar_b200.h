@@ -81,7 +81,18 @@ typedef struct SoarRastGrads {
   float* dL_dviewmat;   /* [16]  nonzero only when config[3] > 0                */
   float* dL_dprojmat;   /* [16]                                                 */
   float* dL_dcampos;    /* [3]                                                  */
+  /* Extension: bit SOAR_ACC_* set = ADD this view's gradient to what the buffer already holds
+   * (culled Gaussians then write nothing) instead of overwriting it. 0 = reference behaviour. */
+  uint32_t accumulate_mask;
 } SoarRastGrads;
+#define SOAR_ACC_MEANS2D   (1u << 0)
+#define SOAR_ACC_COLORS    (1u << 1)
+#define SOAR_ACC_OPACITY   (1u << 2)
+#define SOAR_ACC_MEANS3D   (1u << 3)
+#define SOAR_ACC_COV3D     (1u << 4)
+#define SOAR_ACC_SH        (1u << 5)
+#define SOAR_ACC_SCALES    (1u << 6)
+#define SOAR_ACC_ROTATIONS (1u << 7)
 
 /* ---- rasterizer (replaces DGR `_C.rasterize_gaussians`, DGR/ext.cpp:16 ->
  *      RasterizeGaussiansCUDA -> CudaRasterizer::Rasterizer::forward,
@@ -100,6 +111,16 @@ size_t soar_rast_binning_bytes(uint32_t num_rendered, int32_t width, int32_t hei
  * at the same point, rasterizer_impl.cu:250). */
 int soar_rast_forward_bin(const SoarRastView* view, void* geom, size_t geom_bytes,
                           int32_t* radii, uint32_t* num_rendered_host, soar_stream_t stream);
+
+/* Same as soar_rast_forward_bin without the host synchronisation: the count (and, when
+ * view->prefiltered, the error flag in word 1) are copied asynchronously into
+ * status_pinned_host[2], which must be page-locked host memory that stays valid until `stream`
+ * has passed this point. A multi-view step enqueues phase 1 of ALL its views first and only
+ * then waits for the first count, so the device never idles behind the host. The caller checks
+ * word 1 (non-zero = SOAR_E_PREFILTER) after synchronising. */
+int soar_rast_forward_bin_async(const SoarRastView* view, void* geom, size_t geom_bytes,
+                                int32_t* radii, uint32_t* status_pinned_host,
+                                soar_stream_t stream);
 
 /* Phase 2 (K3..K6): (tile, Gaussian) pair emission in depth order, stable
  * onesweep radix sort over the tile bits, tile ranges, tile alpha-blend. The

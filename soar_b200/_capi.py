@@ -60,7 +60,12 @@ class SoarRastGrads(Structure):
         ("dL_dviewmat", c_void_p),
         ("dL_dprojmat", c_void_p),
         ("dL_dcampos", c_void_p),
+        ("accumulate_mask", c_uint32),
     ]
+
+
+ACC_MEANS2D, ACC_COLORS, ACC_OPACITY, ACC_MEANS3D = 1, 2, 4, 8
+ACC_COV3D, ACC_SH, ACC_SCALES, ACC_ROTATIONS = 16, 32, 64, 128
 
 
 class SoarSmplxModel(Structure):
@@ -85,6 +90,10 @@ SIGNATURES = {
     "soar_rast_forward_bin": (
         c_int32,
         [POINTER(SoarRastView), c_void_p, c_size_t, c_void_p, POINTER(c_uint32), c_void_p],
+    ),
+    "soar_rast_forward_bin_async": (
+        c_int32,
+        [POINTER(SoarRastView), c_void_p, c_size_t, c_void_p, c_void_p, c_void_p],
     ),
     "soar_rast_forward_render": (
         c_int32,

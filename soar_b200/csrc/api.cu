@@ -94,13 +94,13 @@ size_t soar_rast_backward_scratch_bytes(int32_t P) {
   return align_up((size_t)(P < 0 ? 0 : P) * GACC_FLOATS * sizeof(float), 256) + 256;
 }
 
-int soar_rast_forward_bin(const SoarRastView* v, void* geom, size_t geom_bytes, int32_t* radii,
-                          uint32_t* num_rendered_host, soar_stream_t stream_) {
+int soar_rast_forward_bin_async(const SoarRastView* v, void* geom, size_t geom_bytes, int32_t* radii,
+                                uint32_t* status_host, soar_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   int rc = check_view(v, "soar_rast_forward_bin");
   if (rc) return rc;
-  if (!num_rendered_host) { set_error("forward_bin: num_rendered_host is NULL"); return SOAR_E_INVALID; }
-  *num_rendered_host = 0;
+  if (!status_host) { set_error("forward_bin: the host status pointer is NULL"); return SOAR_E_INVALID; }
+  status_host[0] = 0; status_host[1] = 0;
   if (v->P == 0) return SOAR_OK;
   const GeomLayout L = geom_layout(v->P);
   if (!geom || geom_bytes < L.total) {
@@ -152,19 +152,30 @@ int soar_rast_forward_bin(const SoarRastView* v, void* geom, size_t geom_bytes, 
   uint32_t* offsets = reinterpret_cast<uint32_t*>(at(geom, L.point_offsets));
   rc = launch_scan(a.tiles_touched, perm[dsorted], offsets, v->P, at(geom, L.scan_status), stream);
   if (rc) return rc;
-  // the one host sync of the forward (reference: rasterizer_impl.cu:250)
-  uint32_t flag = 0;
-  SOAR_CUDA_TRY(cudaMemcpyAsync(num_rendered_host, offsets + (v->P - 1), sizeof(uint32_t),
+  SOAR_CUDA_TRY(cudaMemcpyAsync(status_host, offsets + (v->P - 1), sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, stream));
   if (v->prefiltered)
-    SOAR_CUDA_TRY(cudaMemcpyAsync(&flag, tail + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
-  SOAR_CUDA_TRY(cudaStreamSynchronize(stream));
-  if (flag) {
+    SOAR_CUDA_TRY(cudaMemcpyAsync(status_host + 1, tail + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                  stream));
+  return SOAR_OK;
+}
+
+int soar_rast_forward_bin(const SoarRastView* v, void* geom, size_t geom_bytes, int32_t* radii,
+                          uint32_t* num_rendered_host, soar_stream_t stream_) {
+  if (!num_rendered_host) { set_error("forward_bin: num_rendered_host is NULL"); return SOAR_E_INVALID; }
+  uint32_t status[2] = {0u, 0u};
+  const int rc = soar_rast_forward_bin_async(v, geom, geom_bytes, radii, status, stream_);
+  if (rc) return rc;
+  // the one host sync of the forward (reference: rasterizer_impl.cu:250)
+  SOAR_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream_));
+  *num_rendered_host = status[0];
+  if (status[1]) {
     set_error("Point is filtered although prefiltered is set. This shouldn't happen!");
     return SOAR_E_PREFILTER;
   }
   return SOAR_OK;
 }
+
 
 int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
                              size_t binning_bytes, void* img, size_t img_bytes,

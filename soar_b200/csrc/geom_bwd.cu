@@ -25,6 +25,19 @@ __device__ __forceinline__ void warp_atomic_add(float* dst, float v) {
   if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(dst, v);
 }
 
+// Gradient stores. With the tensor's bit set in SoarRastGrads.accumulate_mask the value is added to
+// what the caller's buffer already holds (multi-view steps accumulate every view straight into the
+// flat all-reduce buffer instead of going through a separate add kernel per tensor per view) and
+// culled Gaussians write nothing at all.
+__device__ __forceinline__ void put(float* p, float v, bool acc) { *p = acc ? *p + v : v; }
+__device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
+  if (acc) {
+    const float4 o = *p;
+    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+  }
+  *p = v;
+}
+
 // SHV: SH coefficients per Gaussian moved with 16-byte loads/stores (16 or 4; rows are then
 // 192 / 48 bytes, 16-byte aligned); 0 = generic scalar path for any M.
 template <bool LRN_CAM, int SHV>
@@ -35,6 +48,11 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in_range = idx < a.P;
   const bool visible = in_range && a.radii[idx] > 0;
+  const uint32_t accm = a.g.accumulate_mask;
+  const bool acc_m2d = accm & SOAR_ACC_MEANS2D, acc_col = accm & SOAR_ACC_COLORS,
+             acc_opa = accm & SOAR_ACC_OPACITY, acc_m3d = accm & SOAR_ACC_MEANS3D,
+             acc_cov = accm & SOAR_ACC_COV3D, acc_sh = accm & SOAR_ACC_SH,
+             acc_scl = accm & SOAR_ACC_SCALES, acc_rot = accm & SOAR_ACC_ROTATIONS;
   const float* __restrict__ view = a.viewmatrix;
   const float* __restrict__ proj = a.projmatrix;
 
@@ -48,16 +66,18 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
   if (in_range && !visible) {
     // culled: every gradient is exactly zero
     float* p;
-    p = a.g.dL_dmeans2D + 3 * (size_t)idx; p[0] = p[1] = p[2] = 0.f;
-    p = a.g.dL_dcolors + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f;
-    a.g.dL_dopacity[idx] = 0.f;
-    p = a.g.dL_dmeans3D + 3 * (size_t)idx; p[0] = p[1] = p[2] = 0.f;
-    p = a.g.dL_dcov3D + 6 * (size_t)idx;
+    if (!acc_m2d) { p = a.g.dL_dmeans2D + 3 * (size_t)idx; p[0] = p[1] = p[2] = 0.f; }
+    if (!acc_col) { p = a.g.dL_dcolors + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f; }
+    if (!acc_opa) a.g.dL_dopacity[idx] = 0.f;
+    if (!acc_m3d) { p = a.g.dL_dmeans3D + 3 * (size_t)idx; p[0] = p[1] = p[2] = 0.f; }
+    if (!acc_cov) {
+      p = a.g.dL_dcov3D + 6 * (size_t)idx;
 #pragma unroll
-    for (int i = 0; i < 6; ++i) p[i] = 0.f;
-    p = a.g.dL_dscales + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f;
-    reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (a.M > 0 && a.g.dL_dsh) {
+      for (int i = 0; i < 6; ++i) p[i] = 0.f;
+    }
+    if (!acc_scl) { p = a.g.dL_dscales + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f; }
+    if (!acc_rot) reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.M > 0 && a.g.dL_dsh && !acc_sh) {
       if (SHV > 0) {
         float4* p4 = reinterpret_cast<float4*>(a.g.dL_dsh + (size_t)idx * SHV * 3);
 #pragma unroll
@@ -98,10 +118,11 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
 
     {
       float* p = a.g.dL_dmeans2D + 3 * (size_t)idx;
-      p[0] = dL_dmean2d.x; p[1] = dL_dmean2d.y; p[2] = 0.f;
+      put(p, dL_dmean2d.x, acc_m2d); put(p + 1, dL_dmean2d.y, acc_m2d);
+      if (!acc_m2d) p[2] = 0.f;
       p = a.g.dL_dcolors + 3 * (size_t)idx;
-      p[0] = dL_dcolor[0]; p[1] = dL_dcolor[1]; p[2] = dL_dcolor[2];
-      a.g.dL_dopacity[idx] = dL_dopac;
+      put(p, dL_dcolor[0], acc_col); put(p + 1, dL_dcolor[1], acc_col); put(p + 2, dL_dcolor[2], acc_col);
+      put(a.g.dL_dopacity + idx, dL_dopac, acc_opa);
     }
 
     const float3 mean = {a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]};
@@ -223,7 +244,7 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
     {
       float* p = a.g.dL_dcov3D + 6 * (size_t)idx;
 #pragma unroll
-      for (int i = 0; i < 6; ++i) p[i] = dL_dcov[i];
+      for (int i = 0; i < 6; ++i) put(p + i, dL_dcov[i], acc_cov);
     }
 
     // ---- projection + depth terms (backward.cu:464-496) ------------------------------
@@ -355,14 +376,14 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
         float4* d4 = reinterpret_cast<float4*>(dsh);
 #pragma unroll
         for (int i = 0; i < SHV * 3 / 4; ++i)
-          d4[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+          put4(d4 + i, make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]), acc_sh);
       } else {
         const int active = (Deg + 1) * (Deg + 1);
         for (int i = 0; i < a.M; ++i) {
           const float b = (i < active && i < 16) ? basis[i] : 0.f;
-          dsh[3 * i + 0] = b * dRGB[0];
-          dsh[3 * i + 1] = b * dRGB[1];
-          dsh[3 * i + 2] = b * dRGB[2];
+          put(dsh + 3 * i + 0, b * dRGB[0], acc_sh);
+          put(dsh + 3 * i + 1, b * dRGB[1], acc_sh);
+          put(dsh + 3 * i + 2, b * dRGB[2], acc_sh);
         }
       }
       const float3 dL_ddir = {dx[0] * dRGB[0] + dx[1] * dRGB[1] + dx[2] * dRGB[2],
@@ -389,7 +410,8 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
     }
     {
       float* p = a.g.dL_dmeans3D + 3 * (size_t)idx;
-      p[0] = dL_dmean_total.x; p[1] = dL_dmean_total.y; p[2] = dL_dmean_total.z;
+      put(p, dL_dmean_total.x, acc_m3d); put(p + 1, dL_dmean_total.y, acc_m3d);
+      put(p + 2, dL_dmean_total.z, acc_m3d);
     }
 
     // ---- scale / rotation backward (backward.cu:326-432) -------------------------------
@@ -421,7 +443,7 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
                            Rt.m[2][2] * dL_dMt.m[2][2];
       {
         float* p = a.g.dL_dscales + 3 * (size_t)idx;
-        p[0] = ds.x; p[1] = ds.y; p[2] = ds.z;
+        put(p, ds.x, acc_scl); put(p + 1, ds.y, acc_scl); put(p + 2, ds.z, acc_scl);
       }
 
       Mat3 dL_dRt = dL_dMt;
@@ -459,11 +481,13 @@ __global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
              2 * z * (G.m[1][2] + G.m[2][1]) - 4 * y * (G.m[2][2] + G.m[0][0]);
       dq.w = 2 * r * (G.m[0][1] - G.m[1][0]) + 2 * x * (G.m[2][0] + G.m[0][2]) +
              2 * y * (G.m[1][2] + G.m[2][1]) - 4 * z * (G.m[1][1] + G.m[0][0]);
-      reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = dq;
+      put4(reinterpret_cast<float4*>(a.g.dL_drotations) + idx, dq, acc_rot);
     } else {
-      float* p = a.g.dL_dscales + 3 * (size_t)idx;
-      p[0] = p[1] = p[2] = 0.f;
-      reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!acc_scl) {
+        float* p = a.g.dL_dscales + 3 * (size_t)idx;
+        p[0] = p[1] = p[2] = 0.f;
+      }
+      if (!acc_rot) reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
 

@@ -34,6 +34,41 @@ def shard_views(n_views: int, rank: int, world_size: int, costs: Sequence[float]
     return sorted(mine)
 
 
+def iter_views(rasterizers, calls):
+    """Render several views of the same Gaussians back to back without idling the device.
+
+    `rasterizers`: GaussianRasterizer modules (one per view); `calls`: one dict of forward()
+    keyword arguments per view. The first phase of EVERY view (preprocess, depth sort, tile
+    counts) is enqueued up front (GaussianRasterizer.begin), then the views are finished and
+    yielded one at a time — `for out in iter_views(...): loss(out).backward()` keeps only one
+    view's images and binning buffers alive. The reference's loop
+    (TS/renderer/gaussian_batch_renderer.py:273-323) blocks the host once per view on
+    num_rendered (rasterizer_impl.cu:250) with nothing queued behind it; here only the first
+    view of a step waits."""
+    rasterizers, calls = list(rasterizers), list(calls)
+    for r, kw in zip(rasterizers, calls):
+        r.begin(**kw)
+    for r, kw in zip(rasterizers, calls):
+        yield r(**kw)
+
+
+# data_ptr of a registered leaf parameter -> (shape, its slice of a FlatGrads buffer). While a
+# FlatGrads.direct() context is active, the rasterizer backward ADDS the gradients of registered
+# leaves straight into these slices (SoarRastGrads.accumulate_mask) and hands autograd `None` for
+# them: no per-view gradient tensors, no AccumulateGrad add kernels.
+_DIRECT = {}
+
+
+def direct_sink(t):
+    """The accumulation buffer registered for tensor `t`, or None."""
+    if not _DIRECT or t is None or t.numel() == 0 or not t.requires_grad:
+        return None
+    hit = _DIRECT.get(t.data_ptr())
+    if hit is None or hit[0] != tuple(t.shape) or not t.is_contiguous():
+        return None
+    return hit[1]
+
+
 class FlatGrads:
     """One contiguous fp32 buffer holding the gradients of all Gaussian parameters.
 
@@ -62,6 +97,12 @@ class FlatGrads:
     def zero_(self):
         self.flat.zero_()
 
+    def direct(self):
+        """Context manager: inside it, rasterizer backward passes accumulate the gradients of
+        these parameters in place into the flat buffer (single stream; the buffer must have been
+        zeroed for the step). Gradients of anything else flow through autograd as usual."""
+        return _Direct(self)
+
     def grad(self, name: str) -> torch.Tensor:
         a, b = self.slices[name]
         return self.flat[a:b].view_as(self.params[name])
@@ -74,3 +115,22 @@ class FlatGrads:
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
             return None
         return dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, async_op=async_op)
+
+
+class _Direct:
+    def __init__(self, fg):
+        self.fg = fg
+        self.keys = []
+
+    def __enter__(self):
+        for k in self.fg.names:
+            p = self.fg.params[k]
+            if p.is_cuda and p.is_contiguous():
+                _DIRECT[p.data_ptr()] = (tuple(p.shape), self.fg.grad(k))
+                self.keys.append(p.data_ptr())
+        return self.fg
+
+    def __exit__(self, *exc):
+        for k in self.keys:
+            _DIRECT.pop(k, None)
+        return False
