@@ -218,6 +218,32 @@ int soar_smplx_forward(const SoarSmplxModel* model, const float* betas, const fl
                        float* out_joints, float* out_A, float* out_bones, void* workspace,
                        size_t workspace_bytes, soar_stream_t stream);
 
+/* ---- image-space post-ops of the surfel renderer (replaces the torch op chains
+ *      depth2normal / normal2curv, TS/renderer/diff_gaussian_rasterizer.py:359-448, and the
+ *      renderer's post block at :292-303) -------------------------------------------------- */
+typedef struct SoarPostArgs {
+  int32_t width, height;
+  float cx, cy;            /* prcppoint[0]*width, prcppoint[1]*height (:375-376)              */
+  float kinv_x, kinv_y;    /* 1/fov2focal(FoVy, height), 1/fov2focal(FoVx, width) — the
+                            * reference's K00/K11 pairing, kept (:378-382)                    */
+  float mask_threshold;    /* mask = opac > threshold when `mask` is NULL (1e-5 at :292)      */
+  int32_t surfel;          /* 0: the two functions as defined; 1: the renderer's post block:
+                            * channels 1,2 negated, (x+1)/2, normal gradient cut off-mask     */
+  const uint8_t* mask;     /* [H,W] bool, or NULL                                             */
+  const float* opac;       /* [H,W], used when mask is NULL                                   */
+  const float* normal;     /* [3,H,W] or NULL (no curvature / normal output)                  */
+  const float* depth;      /* [H,W] or NULL (no depth normal)                                 */
+} SoarPostArgs;
+/* One launch. Outputs (each may be NULL): out_normal[3,H,W] (surfel only), out_curv[H,W],
+ * out_depth_normal[3,H,W], out_mask[H,W] (bool). */
+int soar_post_forward(const SoarPostArgs* args, float* out_normal, float* out_curv,
+                      float* out_depth_normal, uint8_t* out_mask, soar_stream_t stream);
+/* One launch, deterministic gather (no atomics). Incoming gradients may be NULL (= zero);
+ * dL_dnormal[3,H,W] / dL_ddepth[H,W] are fully written when given. */
+int soar_post_backward(const SoarPostArgs* args, const float* dL_dout_normal, const float* dL_dcurv,
+                       const float* dL_ddepth_normal, float* dL_dnormal, float* dL_ddepth,
+                       soar_stream_t stream);
+
 /* ---- launch accounting / event timing (used by bench.py; no reference analogue:
  *      the reference has an unused CUDA-event Timer, TS/utils/cuda_utils.cu:18-42) --- */
 /* Number of kernels this library has launched in this process. */

@@ -82,6 +82,23 @@ class SoarSmplxModel(Structure):
     ]
 
 
+class SoarPostArgs(Structure):
+    _fields_ = [
+        ("width", c_int32),
+        ("height", c_int32),
+        ("cx", c_float),
+        ("cy", c_float),
+        ("kinv_x", c_float),
+        ("kinv_y", c_float),
+        ("mask_threshold", c_float),
+        ("surfel", c_int32),
+        ("mask", c_void_p),
+        ("opac", c_void_p),
+        ("normal", c_void_p),
+        ("depth", c_void_p),
+    ]
+
+
 # name -> (restype, argtypes); mirrors include/soar_b200.h one to one
 SIGNATURES = {
     "soar_rast_geom_bytes": (c_size_t, [c_int32]),
@@ -136,6 +153,14 @@ SIGNATURES = {
         c_int32,
         [POINTER(SoarSmplxModel), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
          c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "soar_post_forward": (
+        c_int32,
+        [POINTER(SoarPostArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_post_backward": (
+        c_int32,
+        [POINTER(SoarPostArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
     "soar_launch_count": (ctypes.c_ulonglong, []),
     "soar_prof_enable": (None, [c_int32]),

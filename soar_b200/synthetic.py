@@ -229,3 +229,42 @@ def smplx_pose(NB=20, seed=0, global_orient_zero=True):
     if global_orient_zero:
         pose[0] = 0.0
     return dict(betas=_t(betas), full_pose=_t(pose.reshape(1, -1)), transl=_t([[0.0, 0.3, 0.0]]))
+
+
+class ImageCamera:
+    """The five camera attributes the image-space post-ops read (the reference passes its
+    Camera NamedTuple, TS/renderer/gaussian_batch_renderer.py:73-83)."""
+
+    def __init__(self, W, H, fovx, fovy, prcppoint=(0.5, 0.5)):
+        self.image_width, self.image_height = int(W), int(H)
+        self.FoVx, self.FoVy = float(fovx), float(fovy)
+        self.prcppoint = _t(np.asarray(prcppoint))
+
+
+def postops_problem(W, H, seed=0, prcppoint=(0.5, 0.5), fovy_deg=40.0, touch_border=False):
+    """Rasterizer-shaped image outputs for the post-ops (row f2): a bumpy blob seen from ~2.7 m —
+    `opac` [1,H,W] exactly 0 outside a wobbly silhouette (with a hole) and in (0.2, 1] inside,
+    `depth` [1,H,W] smooth + noise inside, 0 outside, `normal` [3,H,W] roughly unit inside.
+    touch_border=True lets the silhouette run over the image border (replicate-padding paths).
+    Plus N(0,1) cotangents for normal / curv / depth_normal."""
+    rng = np.random.Generator(np.random.PCG64(seed + 7919))
+    ys, xs = np.meshgrid(np.arange(H, dtype=np.float64), np.arange(W, dtype=np.float64), indexing="ij")
+    cx, cy = (0.5 * W, 0.5 * H) if not touch_border else (0.3 * W, 0.65 * H)
+    rad = (0.36 if not touch_border else 0.6) * min(W, H)
+    ang = np.arctan2(ys - cy, xs - cx)
+    rr = np.hypot(xs - cx, ys - cy) / (rad * (1 + 0.15 * np.sin(5 * ang + rng.uniform(0, 6.28))))
+    inside = (rr < 1.0) & ~(np.hypot(xs - cx - 0.3 * rad, ys - cy + 0.2 * rad) < 0.12 * rad)
+    inside &= rng.uniform(size=(H, W)) > 0.01          # pin holes
+    z = np.sqrt(np.clip(1.0 - rr * rr, 0.0, None))
+    depth = 2.7 - 0.5 * z + 0.02 * np.sin(xs * 0.21) * np.cos(ys * 0.17) + rng.normal(size=(H, W)) * 2e-3
+    n = np.stack([(xs - cx) / rad, (ys - cy) / rad, -z - 0.2], 0) + rng.normal(size=(3, H, W)) * 0.05
+    n /= np.linalg.norm(n, axis=0, keepdims=True)
+    n *= 1.0 + rng.normal(size=(1, H, W)) * 0.02       # blended normals are not exactly unit
+    opac = np.where(inside, np.clip(1.2 - rr, 0.2, 1.0), 0.0)
+    fovy = math.radians(fovy_deg)
+    fovx = 2 * math.atan(math.tan(fovy / 2) * W / H)
+    return dict(
+        normal=_t(n * inside), depth=_t((depth * inside)[None]), opac=_t(opac[None]),
+        camera=ImageCamera(W, H, fovx, fovy, prcppoint),
+        g_normal=_t(rng.normal(size=(3, H, W))), g_curv=_t(rng.normal(size=(1, H, W))),
+        g_depth_normal=_t(rng.normal(size=(3, H, W))))
