@@ -522,6 +522,67 @@ def lbs_report(device, cpu=True, n=100_000):
     return rep
 
 
+def postops_report(device, W=1024, H=1024, iters=50, cpu=True):
+    """Row f2 stage report at the bench resolution: the renderer's post block (depth2normal +
+    normal2curv + flips, fwd+bwd) — our two stencil launches against the reference's torch op chain
+    (oracle/postops_oracle.py, pinned to the reference's functions) on the same B200 and on the host
+    cores. CUDA events; inputs resident."""
+    from soar_b200 import postops, synthetic
+    from oracle import postops_oracle
+    pb = synthetic.postops_problem(W, H, seed=0, touch_border=True)
+    cam = pb["camera"]
+    dev = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in pb.items()}
+
+    def run(fn, t):
+        n = t["normal"].clone().requires_grad_(True)
+        d = t["depth"].clone().requires_grad_(True)
+        on, oc, od, _ = fn(n, d, t["opac"], cam)
+        ((on * t["g_normal"]).sum() + (oc * t["g_curv"]).sum() + (od * t["g_depth_normal"]).sum()).backward()
+        return n.grad, d.grad
+
+    def time_gpu(fn):
+        for _ in range(5):
+            run(fn, dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(device)
+        e0.record()
+        for _ in range(iters):
+            run(fn, dev)
+        e1.record()
+        torch.cuda.synchronize(device)
+        return e0.elapsed_time(e1) / iters
+
+    # kernel-only time of the two launches (soar_prof events)
+    from soar_b200 import _capi
+    lib = _capi.load()
+    lib.soar_prof_enable(1)
+    for _ in range(iters):
+        run(postops.surfel_postprocess, dev)
+    n = 32
+    counts, ms = (ctypes.c_int32 * n)(), (ctypes.c_float * n)()
+    k = lib.soar_prof_summary(n, counts, ms)
+    kern = {lib.soar_kernel_name(i).decode(): ms[i] / counts[i] for i in range(k) if counts[i]}
+    lib.soar_prof_enable(0)
+    ours = time_gpu(postops.surfel_postprocess)
+    chain = time_gpu(postops_oracle.surfel_postprocess)
+    npix = W * H
+    out = {"workload": f"f2: surfel post block fwd+bwd at {W}x{H} (incl. the autograd loss glue both arms share)",
+           "gpu_ms": ours, "torch_chain_same_gpu_ms": chain, "speedup_vs_torch_chain": chain / ours,
+           "post_fwd_us": kern.get("post_fwd", 0) * 1e3, "post_bwd_us": kern.get("post_bwd", 0) * 1e3,
+           "post_fwd_GBps": npix * 49 / (kern["post_fwd"] * 1e-3) / 1e9 if kern.get("post_fwd") else None,
+           "post_bwd_GBps": npix * 61 / (kern["post_bwd"] * 1e-3) / 1e9 if kern.get("post_bwd") else None,
+           "algorithmic_bytes_per_pixel": {"fwd": 49, "bwd": 61}}
+    if cpu:
+        run(postops_oracle.surfel_postprocess, pb)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            run(postops_oracle.surfel_postprocess, pb)
+        out["cpu_ms"] = (time.perf_counter() - t0) / 3 * 1e3
+        out["cpu_cores"] = torch.get_num_threads()
+        out["cpu_kind"] = "port (oracle/postops_oracle.py, pinned to the reference's own functions)"
+    return out
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -601,6 +662,10 @@ def main():
     if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
         lbs = lbs_report(device, cpu=not args.no_cpu_baseline)
 
+    post = None
+    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
+        post = postops_report(device, wl.W, wl.H, cpu=not args.no_cpu_baseline)
+
     if rank == 0:
         line = {
             "metric": "splat fwd+bwd frames/sec", "value": value, "unit": "frames/s", "n_gpus": world,
@@ -618,7 +683,7 @@ def main():
                        "P_visible": Pv, "num_rendered": R,
                        "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,
-            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs,
+            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post,
         }
         if args.impl == "reference":
             line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",

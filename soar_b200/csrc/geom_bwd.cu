@@ -40,8 +40,11 @@ __device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
 
 // SHV: SH coefficients per Gaussian moved with 16-byte loads/stores (16 or 4; rows are then
 // 192 / 48 bytes, 16-byte aligned); 0 = generic scalar path for any M.
+// 128 threads x 4 CTAs/SM under a 128-register cap (16 B of spill): twice the loads in flight of
+// the uncapped 154-register build, which ran one 256-thread CTA per SM and stalled on the long scoreboard.
+constexpr int GB_THREADS = 128;
 template <bool LRN_CAM, int SHV>
-__global__ void __launch_bounds__(256) geom_bwd_kernel(const GeomBwdArgs a) {
+__global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdArgs a) {
   // config lives on the device: both variants are launched, the one that does
   // not match config[3] (lrn_cam) retires immediately.
   if ((a.config[3] > 0) != LRN_CAM) return;
@@ -508,21 +511,21 @@ int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dprojmat, 0, 16 * sizeof(float), stream));
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dcampos, 0, 3 * sizeof(float), stream));
   if (a.P <= 0) return SOAR_OK;
-  const int grid = ceil_div(a.P, 256);
+  const int grid = ceil_div(a.P, GB_THREADS);
   const bool aligned = a.shs != nullptr && a.g.dL_dsh != nullptr &&
                        ((reinterpret_cast<uintptr_t>(a.shs) | reinterpret_cast<uintptr_t>(a.g.dL_dsh)) & 15u) == 0;
   const int shv = (aligned && a.M == 16) ? 16 : (aligned && a.M == 4 ? 4 : 0);
   {
     KernelScope ks(K_GEOM_BWD, stream);
-    if (shv == 16) geom_bwd_kernel<false, 16><<<grid, 256, 0, stream>>>(a);
-    else if (shv == 4) geom_bwd_kernel<false, 4><<<grid, 256, 0, stream>>>(a);
-    else geom_bwd_kernel<false, 0><<<grid, 256, 0, stream>>>(a);
+    if (shv == 16) geom_bwd_kernel<false, 16><<<grid, GB_THREADS, 0, stream>>>(a);
+    else if (shv == 4) geom_bwd_kernel<false, 4><<<grid, GB_THREADS, 0, stream>>>(a);
+    else geom_bwd_kernel<false, 0><<<grid, GB_THREADS, 0, stream>>>(a);
   }
   {
     KernelScope ks(K_GEOM_BWD, stream);
-    if (shv == 16) geom_bwd_kernel<true, 16><<<grid, 256, 0, stream>>>(a);
-    else if (shv == 4) geom_bwd_kernel<true, 4><<<grid, 256, 0, stream>>>(a);
-    else geom_bwd_kernel<true, 0><<<grid, 256, 0, stream>>>(a);
+    if (shv == 16) geom_bwd_kernel<true, 16><<<grid, GB_THREADS, 0, stream>>>(a);
+    else if (shv == 4) geom_bwd_kernel<true, 4><<<grid, GB_THREADS, 0, stream>>>(a);
+    else geom_bwd_kernel<true, 0><<<grid, GB_THREADS, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("geom_bwd_kernel");
   return SOAR_OK;

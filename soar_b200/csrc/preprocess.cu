@@ -18,8 +18,11 @@ namespace soar {
 
 
 // SHV: SH coefficients per Gaussian fetched with 16-byte loads (16 or 4); 0 = scalar path.
+// 128 threads x 6 CTAs/SM under an 85-register cap (28 B of spill): 768 threads of loads in flight per SM
+// instead of 512 (the uncapped build takes 89 registers).
+constexpr int PP_THREADS = 128;
 template <int SHV>
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(const PreprocessArgs a) {
+__global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const PreprocessArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
 
@@ -159,9 +162,9 @@ int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream) {
   {
     KernelScope ks(K_PREPROCESS, stream);
     const bool aligned = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;
-    if (aligned && a.M == 16) preprocess_fwd_kernel<16><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
-    else if (aligned && a.M == 4) preprocess_fwd_kernel<4><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
-    else preprocess_fwd_kernel<0><<<ceil_div(a.P, 256), 256, 0, stream>>>(a);
+    if (aligned && a.M == 16) preprocess_fwd_kernel<16><<<ceil_div(a.P, PP_THREADS), PP_THREADS, 0, stream>>>(a);
+    else if (aligned && a.M == 4) preprocess_fwd_kernel<4><<<ceil_div(a.P, PP_THREADS), PP_THREADS, 0, stream>>>(a);
+    else preprocess_fwd_kernel<0><<<ceil_div(a.P, PP_THREADS), PP_THREADS, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("preprocess_fwd_kernel");
   return SOAR_OK;
