@@ -268,3 +268,21 @@ def postops_problem(W, H, seed=0, prcppoint=(0.5, 0.5), fovy_deg=40.0, touch_bor
         camera=ImageCamera(W, H, fovx, fovy, prcppoint),
         g_normal=_t(rng.normal(size=(3, H, W))), g_curv=_t(rng.normal(size=(1, H, W))),
         g_depth_normal=_t(rng.normal(size=(3, H, W))))
+
+
+def avatar_gaussians(N, v_template, seed=0):
+    """"avatar" distribution of §8d on the synthetic template: canonical Gaussian centres on the
+    body surface (a random template vertex + N(0, 4 mm) jitter), random unit quaternions (the
+    rotation PARAMETER, scaled so it is not unit: the renderer normalises it), colours U(0,1),
+    occupancy sigmoid(N(0,1)). The in-plane scale is derived from distCUDA2 by the caller
+    (U(0.5,1.5)·sqrt(dist2) clipped to [1e-4, 0.02]), `scale_jitter` holds the U(0.5,1.5) factor."""
+    rng = np.random.Generator(np.random.PCG64(seed + 60013))
+    vt = v_template.numpy() if torch.is_tensor(v_template) else np.asarray(v_template)
+    idx = rng.integers(0, vt.shape[0], size=N)
+    pts = vt[idx] + rng.normal(scale=0.004, size=(N, 3))
+    q = rng.normal(size=(N, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    q *= rng.uniform(0.8, 1.25, size=(N, 1))
+    return dict(points=_t(pts), rot=_t(q), colors=_t(rng.uniform(0.0, 1.0, size=(N, 3))),
+                occ=_t(1.0 / (1.0 + np.exp(-rng.normal(size=(N, 1))))),
+                scale_jitter=_t(rng.uniform(0.5, 1.5, size=(N, 1))))
