@@ -583,6 +583,67 @@ def postops_report(device, W=1024, H=1024, iters=50, cpu=True):
     return out
 
 
+def c5_report(device, N=2_000_000, W=1920, H=1080, iters=5):
+    """BASELINE config 5 on one GPU (a parity-test configuration, reported for scale): one
+    dance_0-shaped step — SMPL-X pose, 30-NN skin-weight query, skinning, surfel rasterizer pass +
+    occupancy pass, post-ops, backward to the canonical Gaussians, and distCUDA2 of the cloud —
+    through soar_b200.avatar.AvatarRenderer. CUDA events; per-kernel sums from soar_prof."""
+    import math as _m
+    from simple_knn._C import distCUDA2
+    from soar_b200 import _capi, synthetic
+    from soar_b200.avatar import AvatarCamera, AvatarRenderer
+    from soar_b200.smplx_fwd import SmplxPoser
+    m = synthetic.smplx_template(NB=10, seed=0)
+    keys = ("v_template", "shapedirs", "posedirs", "J_regressor", "parents", "lbs_weights")
+    poser = SmplxPoser(*(m[k].to(device) for k in keys))
+    ps = {k: v.to(device) for k, v in synthetic.smplx_pose(NB=10, seed=0).items()}
+    cano, _, A0, _ = poser(ps["betas"], torch.zeros_like(ps["full_pose"]), None)
+    ar = AvatarRenderer(poser, cano, torch.linalg.inv(A0))
+    g = {k: v.to(device) for k, v in synthetic.avatar_gaussians(N, cano.cpu(), seed=0).items()}
+    c = synthetic.ring_cameras(1, W, H, seed=0, dist=(1.6, 2.0))[0]
+    cam = AvatarCamera(2 * _m.atan(c["tanfovx"]), 2 * _m.atan(c["tanfovy"]), W, H,
+                       c["viewmatrix"].to(device), c["projmatrix"].to(device), c["campos"].to(device),
+                       torch.tensor([0.5, 0.5], device=device))
+    pts = g["points"].requires_grad_(True)
+    rot = g["rot"].requires_grad_(True)
+    col = g["colors"].requires_grad_(True)
+    bg = torch.zeros(3, device=device)
+    gen = torch.Generator(device).manual_seed(0)
+    cot = {k: torch.randn(ch, H, W, device=device, generator=gen) for k, ch in
+           (("render", 3), ("normal", 3), ("depth", 1), ("mask", 1), ("curv", 1), ("pred_normal", 3))}
+    stats = {}
+
+    def step():
+        d2 = distCUDA2(pts.detach())
+        sc = (g["scale_jitter"] * d2.sqrt()[:, None]).clamp(1e-4, 0.02).requires_grad_(True)
+        bones = ar.pose(ps["betas"], ps["full_pose"], ps["transl"])
+        out = ar.render(pts, rot, ar.weights(pts), bones, col, sc, g["occ"], cam, bg)
+        sum((out[k] * cot[k]).sum() for k in cot).backward()
+        stats["visible"] = out["visibility_filter"]
+        for t in (pts, rot, col):
+            t.grad = None
+
+    step()
+    lib = _capi.load()
+    lib.soar_prof_enable(1)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(device)
+    e0.record()
+    for _ in range(iters):
+        step()
+    e1.record()
+    torch.cuda.synchronize(device)
+    n = 32
+    counts, ms = (ctypes.c_int32 * n)(), (ctypes.c_float * n)()
+    k = lib.soar_prof_summary(n, counts, ms)
+    kern = {lib.soar_kernel_name(i).decode(): round(ms[i] / iters, 4) for i in range(k) if counts[i]}
+    lib.soar_prof_enable(0)
+    return {"workload": f"c5: {N} skinned Gaussians at {W}x{H}: KNN + pose + weight query + skinning + "
+                        "rasterizer pass + occupancy pass + post-ops + backward, 1 GPU",
+            "ms_per_step": e0.elapsed_time(e1) / iters, "visible_fraction": float(stats["visible"].float().mean()),
+            "kernel_ms_per_step": kern, "kernel_ms_sum": round(sum(kern.values()), 3)}
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -666,6 +727,10 @@ def main():
     if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
         post = postops_report(device, wl.W, wl.H, cpu=not args.no_cpu_baseline)
 
+    c5 = None
+    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
+        c5 = c5_report(device)
+
     if rank == 0:
         line = {
             "metric": "splat fwd+bwd frames/sec", "value": value, "unit": "frames/s", "n_gpus": world,
@@ -683,7 +748,7 @@ def main():
                        "P_visible": Pv, "num_rendered": R,
                        "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,
-            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post,
+            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post, "c5_step": c5,
         }
         if args.impl == "reference":
             line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",

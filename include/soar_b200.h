@@ -196,6 +196,16 @@ int soar_lbs_query_weights(const float* points, int32_t N, const float* cano_ver
                            const float* lbs_weights, int32_t J, int32_t K, const float* bones,
                            float* out_weights, float* out_mats, soar_stream_t stream);
 
+/* The same query through a uniform grid over the canonical vertices (exact: identical neighbours,
+ * ties on the vertex index): a few hundred distance evaluations per point instead of V. The grid
+ * is built once per vertex set (they change only when betas change, TS/utils/smpl.py:249-258). */
+size_t soar_lbs_query_grid_bytes(int32_t V);
+int soar_lbs_query_build_grid(const float* cano_vertices, int32_t V, void* grid, size_t grid_bytes,
+                              soar_stream_t stream);
+int soar_lbs_query_weights_grid(const float* points, int32_t N, const void* grid, int32_t V,
+                                const float* lbs_weights, int32_t J, int32_t K, const float* bones,
+                                float* out_weights, float* out_mats, soar_stream_t stream);
+
 /* ---- SMPL-X body-model forward for one pose (replaces smplx.lbs.lbs(),
  *      TS/utils/smplx/lbs.py:147-246, plus the transl fold of SMPLX.forward,
  *      TS/utils/smplx/body_models.py:1380-1383, and the cano->live bones of

@@ -148,6 +148,13 @@ SIGNATURES = {
         [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
          c_void_p, c_void_p],
     ),
+    "soar_lbs_query_grid_bytes": (c_size_t, [c_int32]),
+    "soar_lbs_query_build_grid": (c_int32, [c_void_p, c_int32, c_void_p, c_size_t, c_void_p]),
+    "soar_lbs_query_weights_grid": (
+        c_int32,
+        [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
+         c_void_p, c_void_p],
+    ),
     "soar_smplx_workspace_bytes": (c_size_t, [c_int32, c_int32]),
     "soar_smplx_forward": (
         c_int32,

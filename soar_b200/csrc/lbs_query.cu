@@ -19,6 +19,7 @@
 // table is L2-resident) — 6.6 KB of L2 traffic per point and nothing but the [N, J] result
 // (or the 48-byte blended transform) goes to HBM.
 #include <float.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace soar {
@@ -34,7 +35,12 @@ struct DI {
   uint32_t i;
 };
 __device__ __forceinline__ bool di_less(const DI& a, const DI& b) {
-  return a.d < b.d || (a.d == b.d && a.i < b.i);  // index breaks ties: deterministic
+  // (distance, index) lexicographic, the index breaking ties deterministically. Squared distances
+  // are >= +0 and never NaN here (NaN is rejected before it is queued), so their bit patterns order
+  // like the floats and the pair compares as ONE unsigned 64-bit key (two ISETPs).
+  const unsigned long long ka = ((unsigned long long)__float_as_uint(a.d) << 32) | a.i;
+  const unsigned long long kb = ((unsigned long long)__float_as_uint(b.d) << 32) | b.i;
+  return ka < kb;
 }
 __device__ __forceinline__ DI di_shfl_xor(const DI& a, int m) {
   DI r;
@@ -70,6 +76,60 @@ __device__ __forceinline__ void merge32(DI& best, DI q, uint32_t lane) {
   if (di_less(r, best)) best = r;
 #pragma unroll
   for (int m = 16; m > 0; m >>= 1) cmpx(best, m, (lane & m) == 0);
+}
+
+// inverse-distance blend of the K winners' weight rows (+ optional bone blend), shared epilogue.
+// The 2K row loads go to L2 (the 2.3 MB table is resident there, L1 is mostly carved out as shared
+// memory): they are issued in batches of 8 rows before any is consumed, so a point pays ~4 L2 round
+// trips instead of K. Missing neighbours (lanes with weight 0) read row 0 and add 0.
+__device__ __forceinline__ void lq_epilogue(const DI& best, int K, int n, int J,
+                                            const float* __restrict__ lbs_weights,
+                                            const float* s_bones, float* wrow,
+                                            float* __restrict__ out_weights,
+                                            float* __restrict__ out_mats, uint32_t lane) {
+  const bool valid = lane < (uint32_t)K && best.i != 0xffffffffu;
+  float w = 0.f;
+  if (valid) w = 1.0f / fminf(fmaxf(sqrtf(best.d), 0.0001f), 1.0f);
+  float wsum = w;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
+  w = w / wsum;
+  const uint32_t my_row = valid ? best.i : 0u;
+  const bool c0 = (int)lane < J, c1 = (int)lane + 32 < J;
+  float a0 = 0.f, a1 = 0.f;
+  constexpr int EB = 8;
+  for (int k0 = 0; k0 < K; k0 += EB) {
+    float v0[EB], v1[EB], wk[EB];
+#pragma unroll
+    for (int u = 0; u < EB; ++u) {
+      const int k = min(k0 + u, 31);
+      const uint32_t idx = __shfl_sync(0xffffffffu, my_row, k);
+      wk[u] = (k0 + u < K) ? __shfl_sync(0xffffffffu, w, k) : 0.f;
+      const float* row = lbs_weights + (size_t)idx * J;
+      v0[u] = c0 ? __ldg(row + lane) : 0.f;
+      v1[u] = c1 ? __ldg(row + lane + 32) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < EB; ++u) {
+      a0 += wk[u] * v0[u];
+      a1 += wk[u] * v1[u];
+    }
+  }
+  if (out_weights != nullptr) {
+    if (c0) out_weights[(size_t)n * J + lane] = a0;
+    if (c1) out_weights[(size_t)n * J + lane + 32] = a1;
+  }
+  if (out_mats != nullptr) {
+    wrow[lane] = a0;
+    wrow[lane + 32] = a1;
+    __syncwarp();
+    if (lane < 12) {
+      float acc = 0.f;
+      for (int j = 0; j < J; ++j) acc += wrow[j] * s_bones[12 * j + lane];
+      out_mats[(size_t)n * 12 + lane] = acc;
+    }
+    __syncwarp();
+  }
 }
 
 __global__ void __launch_bounds__(LQ_THREADS, 1)
@@ -155,39 +215,295 @@ lbs_query_kernel(const float* __restrict__ points, int N, const float* __restric
       merge32(best, q, lane);
     }
     __syncwarp();
-    // inverse-distance weights of the K nearest (lanes >= K, or missing neighbours, weigh 0)
-    const bool valid = lane < (uint32_t)K && best.i != 0xffffffffu;
-    float w = 0.f;
-    if (valid) w = 1.0f / fminf(fmaxf(sqrtf(best.d), 0.0001f), 1.0f);
-    float wsum = w;
+    lq_epilogue(best, K, n, J, lbs_weights, s_bones, wrow, out_weights, out_mats, lane);
+  }
+}
+
+// =================================================================================================
+// Grid-accelerated exact query
+// =================================================================================================
+// The brute force above evaluates V = 10,475 distances per point. The canonical vertices are a
+// surface with ~1.4 cm spacing, so the 30 nearest lie within ~4-5 cm: a uniform grid over the
+// vertices (cell edge h ~ 3 cm, chosen from the bounding box and V) cuts that to the few hundred
+// vertices of a (2k+1)^3 block of cells, k growing until the K-th best distance is provably inside
+// the searched cube. Vertices are sorted by cell with x fastest, so one (y, z) row of the block is
+// ONE contiguous run of the sorted arrays. Exactness is kept: the search only stops when
+// tau < (k h (1 - 1e-4))^2 (strictly: equal distances tie-break on the original index) or the cube
+// covers the whole grid; points far outside the body start at the first ring that reaches the grid.
+//
+// Grid blob (device memory, built once per vertex set by soar_lbs_query_build_grid):
+//   LqGridHeader | sorted x[V] | y[V] | z[V] | perm[V] (sorted position -> original index) |
+//   cell_start[cells + 1]
+constexpr int LQ_MAX_CELLS = 1 << 20;
+struct LqGridHeader {
+  float ox, oy, oz, h, inv_h;
+  int nx, ny, nz, V, cells;
+  int pad[6];
+};
+static_assert(sizeof(LqGridHeader) == 64, "LqGridHeader is 64 bytes");
+
+__device__ __forceinline__ int lq_cell(float v, float o, float inv_h, int n) {
+  return min(max((int)floorf((v - o) * inv_h), 0), n - 1);
+}
+
+// One CTA builds the whole grid (V ~ 1e4, cells <= 1M: a one-time ~100 us job per vertex set).
+__global__ void __launch_bounds__(1024) lbs_query_build_kernel(const float* __restrict__ verts, int V,
+                                                               unsigned char* __restrict__ blob,
+                                                               float h_scale) {
+  __shared__ float s_red[6][32];
+  __shared__ LqGridHeader s_h;
+  __shared__ uint32_t s_scan[32];
+  __shared__ uint32_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (int v = tid; v < V; v += 1024)
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wsum += __shfl_xor_sync(0xffffffffu, wsum, o);
-    w = w / wsum;
-    // blend the K weight rows, nearest first; lane owns columns lane and lane + 32
-    float a0 = 0.f, a1 = 0.f;
-    for (int k = 0; k < K; ++k) {
-      const uint32_t idx = __shfl_sync(0xffffffffu, best.i, k);
-      const float wk = __shfl_sync(0xffffffffu, w, k);
-      if (idx == 0xffffffffu) continue;
-      const float* row = lbs_weights + (size_t)idx * J;
-      if ((int)lane < J) a0 += wk * __ldg(row + lane);
-      if ((int)lane + 32 < J) a1 += wk * __ldg(row + lane + 32);
+    for (int a = 0; a < 3; ++a) {
+      const float x = verts[3 * v + a];
+      lo[a] = fminf(lo[a], x); hi[a] = fmaxf(hi[a], x);
     }
-    if (out_weights != nullptr) {
-      if ((int)lane < J) out_weights[(size_t)n * J + lane] = a0;
-      if ((int)lane + 32 < J) out_weights[(size_t)n * J + lane + 32] = a1;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+      hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
     }
-    if (out_mats != nullptr) {
-      wrow[lane] = a0;
-      wrow[lane + 32] = a1;
+    if (lane == 0) { s_red[a][warp] = lo[a]; s_red[3 + a][warp] = hi[a]; }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float L[3], H[3];
+    for (int a = 0; a < 3; ++a) {
+      L[a] = s_red[a][0]; H[a] = s_red[3 + a][0];
+      for (int w = 1; w < 32; ++w) { L[a] = fminf(L[a], s_red[a][w]); H[a] = fmaxf(H[a], s_red[3 + a][w]); }
+    }
+    const float ex = H[0] - L[0], ey = H[1] - L[1], ez = H[2] - L[2];
+    // h ~ 1.2 x the vertex spacing a surface filling the bounding box's faces would have
+    float h = h_scale * sqrtf(2.f * (ex * ey + ey * ez + ez * ex) / (float)V);
+    h = fmaxf(h, 1e-6f * fmaxf(fmaxf(ex, ey), fmaxf(ez, 1e-30f)));
+    if (!(h > 0.f)) h = 1.f;  // all vertices coincide
+    int nx, ny, nz;
+    for (;;) {
+      nx = (int)(ex / h) + 1; ny = (int)(ey / h) + 1; nz = (int)(ez / h) + 1;
+      if ((long long)nx * ny * nz <= LQ_MAX_CELLS) break;
+      h *= 1.26f;
+    }
+    s_h.ox = L[0]; s_h.oy = L[1]; s_h.oz = L[2]; s_h.h = h; s_h.inv_h = 1.f / h;
+    s_h.nx = nx; s_h.ny = ny; s_h.nz = nz; s_h.V = V; s_h.cells = nx * ny * nz;
+    for (int i = 0; i < 6; ++i) s_h.pad[i] = 0;
+    *reinterpret_cast<LqGridHeader*>(blob) = s_h;
+    s_carry = 0;
+  }
+  __syncthreads();
+  const LqGridHeader g = s_h;
+  float* const sx = reinterpret_cast<float*>(blob + sizeof(LqGridHeader));
+  float* const sy = sx + V;
+  float* const sz = sy + V;
+  uint32_t* const perm = reinterpret_cast<uint32_t*>(sz + V);
+  uint32_t* const cell_start = perm + V;  // cells + 1 entries; used as counters, then cursors
+  for (int c = tid; c <= g.cells; c += 1024) cell_start[c] = 0;
+  __syncthreads();
+  for (int v = tid; v < V; v += 1024) {
+    const int cx = lq_cell(verts[3 * v], g.ox, g.inv_h, g.nx), cy = lq_cell(verts[3 * v + 1], g.oy, g.inv_h, g.ny),
+              cz = lq_cell(verts[3 * v + 2], g.oz, g.inv_h, g.nz);
+    atomicAdd(&cell_start[(cz * g.ny + cy) * g.nx + cx], 1u);
+  }
+  __syncthreads();
+  // exclusive scan over the cells, 1024 at a time
+  for (int base = 0; base <= g.cells; base += 1024) {
+    const int c = base + tid;
+    const uint32_t cnt = c <= g.cells ? cell_start[c] : 0u;
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    uint32_t off = s_carry;
+    for (int w = 0; w < warp; ++w) off += s_scan[w];
+    if (c <= g.cells) cell_start[c] = off + incl - cnt;
+    __syncthreads();
+    if (tid == 1023) s_carry = off + incl;
+    __syncthreads();
+  }
+  // scatter; cell_start[c] doubles as the cursor of cell c and ends up as the START of cell c + 1,
+  // so the final table is read shifted by one (start of c = table[c - 1], table[-1] = 0)
+  for (int v = tid; v < V; v += 1024) {
+    const float x = verts[3 * v], y = verts[3 * v + 1], z = verts[3 * v + 2];
+    const int cx = lq_cell(x, g.ox, g.inv_h, g.nx), cy = lq_cell(y, g.oy, g.inv_h, g.ny),
+              cz = lq_cell(z, g.oz, g.inv_h, g.nz);
+    const uint32_t pos = atomicAdd(&cell_start[(cz * g.ny + cy) * g.nx + cx], 1u);
+    sx[pos] = x; sy[pos] = y; sz[pos] = z; perm[pos] = (uint32_t)v;
+  }
+}
+
+// Per-warp selection state: the 32 best so far sorted across the lanes + a queue of candidates.
+struct LqSel {
+  DI best;
+  float tau;
+  uint32_t qn;
+};
+
+// Offer the vertices at sorted positions [s, e) to the selection (whole warp; s, e uniform).
+__device__ __forceinline__ void lq_offer_run(LqSel& st, int s, int e, float px, float py, float pz,
+                                             const float* s_x, const float* s_y, const float* s_z,
+                                             const uint32_t* perm, float* qd, uint32_t* qi,
+                                             int K, uint32_t lane, uint32_t lt) {
+  for (int base = s; base < e; base += 32) {
+    const int v = base + (int)lane;
+    float d = FLT_MAX;
+    if (v < e) {
+      const float dx = px - s_x[v], dy = py - s_y[v], dz = pz - s_z[v];
+      d = dx * dx + dy * dy + dz * dz;
+    }
+    const bool cand = v < e && (d < st.tau || (d == st.tau && st.tau != FLT_MAX));
+    const uint32_t bal = __ballot_sync(0xffffffffu, cand);
+    if (bal == 0) continue;
+    if (cand) {
+      const uint32_t slot = st.qn + __popc(bal & lt);
+      qd[slot] = d;
+      qi[slot] = perm[v];
+    }
+    st.qn += __popc(bal);
+    __syncwarp();
+    if (st.qn >= 32) {
+      DI q;
+      q.d = qd[lane]; q.i = qi[lane];
+      sort32(q, lane);
+      merge32(st.best, q, lane);
+      st.tau = __shfl_sync(0xffffffffu, st.best.d, K - 1);
+      const uint32_t rest = st.qn - 32;
+      float rd = 0.f; uint32_t ri = 0;
+      if (lane < rest) { rd = qd[32 + lane]; ri = qi[32 + lane]; }
       __syncwarp();
-      if (lane < 12) {
-        float acc = 0.f;
-        for (int j = 0; j < J; ++j) acc += wrow[j] * s_bones[12 * j + lane];
-        out_mats[(size_t)n * 12 + lane] = acc;
+      if (lane < rest) { qd[lane] = rd; qi[lane] = ri; }
+      st.qn = rest;
+      __syncwarp();
+    }
+  }
+}
+
+__device__ __forceinline__ void lq_flush(LqSel& st, float* qd, uint32_t* qi, int K, uint32_t lane) {
+  if (st.qn > 0) {
+    DI q;
+    q.d = lane < st.qn ? qd[lane] : FLT_MAX;
+    q.i = lane < st.qn ? qi[lane] : 0xffffffffu;
+    sort32(q, lane);
+    merge32(st.best, q, lane);
+    st.tau = __shfl_sync(0xffffffffu, st.best.d, K - 1);
+    st.qn = 0;
+  }
+  __syncwarp();
+}
+
+// sorted-array range of the cells [x0, x1] of row (y, z); table[c] = END of cell c (build kernel)
+__device__ __forceinline__ void lq_row_range(const uint32_t* __restrict__ table, int nx, int ny, int x0,
+                                             int x1, int y, int z, int& s, int& e) {
+  s = e = 0;
+  if (x0 > x1) return;
+  const int row = (z * ny + y) * nx;
+  const int c0 = row + x0;
+  s = c0 > 0 ? (int)__ldg(table + c0 - 1) : 0;
+  e = (int)__ldg(table + row + x1);
+}
+
+// 24 warps per (persistent, one per SM) CTA; PERM_SMEM: the sorted-position -> vertex-index map is
+// staged in shared memory too (V <= LQG_PERM_SMEM_MAX_V), so pushing a candidate never waits on L2.
+constexpr int LQG_WARPS = 24;
+constexpr int LQG_THREADS = LQG_WARPS * 32;
+constexpr int LQG_PERM_SMEM_MAX_V = 13000;
+template <bool PERM_SMEM>
+__global__ void __launch_bounds__(LQG_THREADS, 1)
+lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
+                      const float* __restrict__ lbs_weights, int J, int K,
+                      const float* __restrict__ bones, float* __restrict__ out_weights,
+                      float* __restrict__ out_mats) {
+  const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
+  const int V = g.V;
+  const float* const gx = reinterpret_cast<const float*>(blob + sizeof(LqGridHeader));
+  const uint32_t* const perm = reinterpret_cast<const uint32_t*>(gx + 3 * (size_t)V);
+  const uint32_t* const table = perm + V;
+  extern __shared__ float s_dyn[];
+  float* const s_x = s_dyn;
+  float* const s_y = s_x + V;
+  float* const s_z = s_y + V;
+  float* const s_bones = s_z + V;
+  float* const s_qd = s_bones + LQ_MAX_J * 12;
+  uint32_t* const s_qi = reinterpret_cast<uint32_t*>(s_qd + LQG_WARPS * 64);
+  float* const s_w = reinterpret_cast<float*>(s_qi + LQG_WARPS * 64);
+  uint32_t* const s_perm = reinterpret_cast<uint32_t*>(s_w + LQG_WARPS * LQ_MAX_J);
+
+  const int tid = threadIdx.x;
+  const uint32_t lane = tid & 31, warp = tid >> 5;
+  for (int v = tid; v < 3 * V; v += LQG_THREADS) s_x[v] = gx[v];  // x | y | z are contiguous
+  if (PERM_SMEM)
+    for (int v = tid; v < V; v += LQG_THREADS) s_perm[v] = perm[v];
+  if (bones != nullptr)
+    for (int i = tid; i < J * 12; i += LQG_THREADS) s_bones[i] = bones[(i / 12) * 16 + (i % 12)];
+  __syncthreads();
+  const uint32_t* const perm_rd = PERM_SMEM ? s_perm : perm;
+
+  float* const qd = s_qd + warp * 64;
+  uint32_t* const qi = s_qi + warp * 64;
+  float* const wrow = s_w + warp * LQ_MAX_J;
+  const uint32_t lt = lanemask_lt();
+  const int BIG = 1 << 20;
+
+  for (int n = blockIdx.x * LQG_WARPS + warp; n < N; n += gridDim.x * LQG_WARPS) {
+    const float px = points[3 * n], py = points[3 * n + 1], pz = points[3 * n + 2];
+    // virtual (unclamped) cell of the point; NaN / huge coordinates land on +-BIG
+    const float fx = floorf((px - g.ox) * g.inv_h), fy = floorf((py - g.oy) * g.inv_h),
+                fz = floorf((pz - g.oz) * g.inv_h);
+    const int cx = fx >= -(float)BIG ? (fx <= (float)BIG ? (int)fx : BIG) : -BIG;
+    const int cy = fy >= -(float)BIG ? (fy <= (float)BIG ? (int)fy : BIG) : -BIG;
+    const int cz = fz >= -(float)BIG ? (fz <= (float)BIG ? (int)fz : BIG) : -BIG;
+    // first ring that reaches the grid
+    const int kmin = max(max(max(-cx, cx - (g.nx - 1)), max(-cy, cy - (g.ny - 1))),
+                         max(max(-cz, cz - (g.nz - 1)), 0));
+    LqSel st;
+    st.best.d = FLT_MAX; st.best.i = 0xffffffffu; st.tau = FLT_MAX; st.qn = 0;
+    int prev = kmin - 1;  // half-width of the cube searched so far (-1: nothing)
+    for (int k = max(kmin, 1);; ++k) {
+      const int x0 = max(cx - k, 0), x1 = min(cx + k, g.nx - 1);
+      const int y0 = max(cy - k, 0), y1 = min(cy + k, g.ny - 1);
+      const int z0 = max(cz - k, 0), z1 = min(cz + k, g.nz - 1);
+      const int nyr = y1 - y0 + 1, nrows = nyr * (z1 - z0 + 1);
+      for (int r0 = 0; r0 < nrows; r0 += 32) {
+        const int r = r0 + (int)lane;
+        int as = 0, ae = 0, bs = 0, be = 0;
+        if (r < nrows) {
+          const int yy = y0 + r % nyr, zz = z0 + r / nyr;
+          const bool inner = prev >= 0 && abs(yy - cy) <= prev && abs(zz - cz) <= prev;
+          if (!inner) {
+            lq_row_range(table, g.nx, g.ny, x0, x1, yy, zz, as, ae);
+          } else {
+            lq_row_range(table, g.nx, g.ny, x0, min(cx - prev - 1, g.nx - 1), yy, zz, as, ae);
+            lq_row_range(table, g.nx, g.ny, max(cx + prev + 1, 0), x1, yy, zz, bs, be);
+          }
+        }
+        uint32_t todo = __ballot_sync(0xffffffffu, ae > as || be > bs);
+        while (todo) {
+          const int src = __ffs(todo) - 1;
+          todo &= todo - 1;
+          const int s0 = __shfl_sync(0xffffffffu, as, src), e0 = __shfl_sync(0xffffffffu, ae, src);
+          const int s1 = __shfl_sync(0xffffffffu, bs, src), e1 = __shfl_sync(0xffffffffu, be, src);
+          lq_offer_run(st, s0, e0, px, py, pz, s_x, s_y, s_z, perm_rd, qd, qi, K, lane, lt);
+          lq_offer_run(st, s1, e1, px, py, pz, s_x, s_y, s_z, perm_rd, qd, qi, K, lane, lt);
+        }
       }
-      __syncwarp();
+      lq_flush(st, qd, qi, K, lane);
+      const bool whole = x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1;
+      if (whole) break;
+      // everything unsearched is at least k cells away along some axis
+      const float reach = (float)k * g.h * 0.9999f;
+      const uint32_t kth = __shfl_sync(0xffffffffu, st.best.i, K - 1);
+      if (kth != 0xffffffffu && st.tau < reach * reach) break;
+      prev = k;
     }
+    lq_epilogue(st.best, K, n, J, lbs_weights, s_bones, wrow, out_weights, out_mats, lane);
   }
 }
 
@@ -229,6 +545,78 @@ int soar_lbs_query_weights(const float* points, int32_t N, const float* cano_ver
                                                          K, bones, out_weights, out_mats);
   }
   SOAR_LAUNCH_CHECK("lbs_query_kernel");
+  return SOAR_OK;
+}
+
+size_t soar_lbs_query_grid_bytes(int32_t V) {
+  if (V <= 0) return 0;
+  return sizeof(LqGridHeader) + (size_t)V * 16 + ((size_t)LQ_MAX_CELLS + 1) * 4;
+}
+
+int soar_lbs_query_build_grid(const float* cano_vertices, int32_t V, void* grid, size_t grid_bytes,
+                              soar_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (V <= 0 || V > LQ_MAX_V) {
+    set_error("soar_lbs_query_build_grid: bad V=%d (1..%d)", V, LQ_MAX_V);
+    return SOAR_E_INVALID;
+  }
+  if (!cano_vertices || !grid) {
+    set_error("soar_lbs_query_build_grid: a required pointer is NULL");
+    return SOAR_E_INVALID;
+  }
+  if (grid_bytes < soar_lbs_query_grid_bytes(V)) {
+    set_error("soar_lbs_query_build_grid: grid buffer of %zu bytes, need %zu", grid_bytes,
+              soar_lbs_query_grid_bytes(V));
+    return SOAR_E_WORKSPACE;
+  }
+  {
+    KernelScope ks(K_LBS_QUERY_BUILD, stream);
+    const char* hs = getenv("SOAR_LQ_HSCALE");  // tuning knob (tools/lq_bench.py); default 1.2
+    const float h_scale = hs ? (float)atof(hs) : 1.2f;
+    lbs_query_build_kernel<<<1, 1024, 0, stream>>>(cano_vertices, V, (unsigned char*)grid,
+                                                   h_scale > 0.f ? h_scale : 1.2f);
+  }
+  SOAR_LAUNCH_CHECK("lbs_query_build_kernel");
+  return SOAR_OK;
+}
+
+int soar_lbs_query_weights_grid(const float* points, int32_t N, const void* grid, int32_t V,
+                                const float* lbs_weights, int32_t J, int32_t K, const float* bones,
+                                float* out_weights, float* out_mats, soar_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (N < 0 || V <= 0 || V > LQ_MAX_V || J <= 0 || J > LQ_MAX_J || K <= 0 || K > LQ_MAX_K) {
+    set_error("soar_lbs_query_weights_grid: bad sizes N=%d V=%d (<= %d) J=%d (<= %d) K=%d (<= %d)", N,
+              V, LQ_MAX_V, J, LQ_MAX_J, K, LQ_MAX_K);
+    return SOAR_E_INVALID;
+  }
+  if (N == 0) return SOAR_OK;
+  if (!points || !grid || !lbs_weights || (!out_weights && !out_mats) || (out_mats && !bones)) {
+    set_error("soar_lbs_query_weights_grid: a required pointer is NULL");
+    return SOAR_E_INVALID;
+  }
+  const bool perm_smem = V <= LQG_PERM_SMEM_MAX_V;
+  const size_t smem = ((size_t)(perm_smem ? 4 : 3) * V + LQ_MAX_J * 12 + LQG_WARPS * 64 * 2 +
+                       LQG_WARPS * LQ_MAX_J) * 4;
+  if (perm_smem)
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_grid_kernel<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  else
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_grid_kernel<false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int dev = 0, sms = 148;
+  SOAR_CUDA_TRY(cudaGetDevice(&dev));
+  SOAR_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid_dim = min(sms, ceil_div(N, LQG_WARPS));
+  {
+    KernelScope ks(K_LBS_QUERY, stream);
+    if (perm_smem)
+      lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats);
+    else
+      lbs_query_grid_kernel<false><<<grid_dim, LQG_THREADS, smem, stream>>>(
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats);
+  }
+  SOAR_LAUNCH_CHECK("lbs_query_grid_kernel");
   return SOAR_OK;
 }
 

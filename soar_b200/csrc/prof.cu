@@ -54,7 +54,7 @@ static const char* kKernelNames[K_COUNT] = {
     "radix_onesweep", "tile_ranges", "blend_fwd", "blend_bwd", "geom_bwd", "knn_bbox",
     "knn_morton", "knn_gather", "knn_boxes", "knn_search", "lbs_fwd", "lbs_bwd", "lbs_query",
     "smplx_shape", "smplx_posedirs", "smplx_joints", "smplx_chain", "smplx_skin", "post_fwd",
-    "post_bwd"};
+    "post_bwd", "lbs_query_build"};
 
 }  // namespace soar
 

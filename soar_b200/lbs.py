@@ -101,6 +101,13 @@ class SkinWeightQuery:
         if self.weights.shape[0] != self.verts.shape[0]:
             raise RuntimeError("SkinWeightQuery: lbs_weights must have one row per canonical vertex")
         self.K = int(K)
+        self.brute_force = False   # True: the V-distances-per-point kernel (kept for ablation)
+        V = self.verts.shape[0]
+        self.grid = torch.empty(_lib.soar_lbs_query_grid_bytes(V), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _capi.check(_lib.soar_lbs_query_build_grid(self.verts.data_ptr(), V, self.grid.data_ptr(),
+                                                       self.grid.numel(), _stream()),
+                        "soar_lbs_query_build_grid")
 
     def _run(self, points, bones, want_weights, want_mats):
         if not points.is_cuda:
@@ -116,10 +123,17 @@ class SkinWeightQuery:
             if b.shape[0] != J:
                 raise RuntimeError(f"SkinWeightQuery: {b.shape[0]} bones for {J} skin-weight columns")
         with torch.cuda.device(dev):
-            _capi.check(_lib.soar_lbs_query_weights(_capi.ptr(pts), N, self.verts.data_ptr(), V,
-                                                    self.weights.data_ptr(), J, self.K, _capi.ptr(b),
-                                                    _capi.ptr(w), _capi.ptr(m), _stream()),
-                        "soar_lbs_query_weights")
+            if self.brute_force:
+                _capi.check(_lib.soar_lbs_query_weights(_capi.ptr(pts), N, self.verts.data_ptr(), V,
+                                                        self.weights.data_ptr(), J, self.K, _capi.ptr(b),
+                                                        _capi.ptr(w), _capi.ptr(m), _stream()),
+                            "soar_lbs_query_weights")
+            else:
+                _capi.check(_lib.soar_lbs_query_weights_grid(_capi.ptr(pts), N, self.grid.data_ptr(), V,
+                                                             self.weights.data_ptr(), J, self.K,
+                                                             _capi.ptr(b), _capi.ptr(w), _capi.ptr(m),
+                                                             _stream()),
+                            "soar_lbs_query_weights_grid")
         return w, m
 
     def __call__(self, points):

@@ -132,3 +132,36 @@ def test_skin_weight_query_rejects_cpu_and_bad_sizes():
     q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda(), K=64)
     with pytest.raises(RuntimeError):
         q(m["v_template"].cuda())
+
+
+@pytest.mark.parametrize("V,K", [(synthetic.N_VERTS, 30), (500, 30), (20, 30), (1, 1), (3000, 7)])
+def test_skin_weight_query_grid_is_bit_identical_to_brute_force(V, K):
+    """The grid search must pick exactly the brute force's neighbours (same order, index
+    tie-break) for points on the body, far outside the bounding box, on duplicated vertices and at
+    non-finite coordinates — the blended weights are then bit-identical."""
+    from soar_b200.lbs import SkinWeightQuery
+    m = synthetic.smplx_template(V=max(V, 2), NB=1, seed=9)
+    verts, lw = m["v_template"][:V].clone(), m["lbs_weights"][:V].clone()
+    if V >= 20:
+        verts[V // 2: V // 2 + 5] = verts[0]          # duplicated vertices: distance ties
+    gen = torch.Generator().manual_seed(V + K)
+    N = 20_000
+    src = verts[torch.randint(0, V, (N,), generator=gen)]
+    pts = src + 0.004 * torch.randn(N, 3, generator=gen)
+    pts[:2000] = src[:2000]                            # exactly on vertices
+    pts[2000:4000] += 0.3 * torch.randn(2000, 3, generator=gen)   # off the body
+    pts[4000:4500] = 50.0 * torch.randn(500, 3, generator=gen)    # far outside the grid
+    pts[4500] = torch.tensor([1e30, 0.0, 0.0])
+    pts[4501] = torch.tensor([-3e38, 3e38, 0.0])
+    q = SkinWeightQuery(verts.cuda(), lw.cuda(), K=K)
+    fast = q(pts.cuda())
+    q.brute_force = True
+    slow = q(pts.cuda())
+    same = (fast == slow) | (fast.isnan() & slow.isnan())
+    assert same.all(), f"{(~same).any(1).sum().item()} of {N} points differ"
+    bones = synthetic.skinning_problem(8, seed=3)["bones"].cuda()
+    q.brute_force = False
+    m_fast = q.mats(pts.cuda(), bones)
+    q.brute_force = True
+    m_slow = q.mats(pts.cuda(), bones)
+    assert ((m_fast == m_slow) | (m_fast.isnan() & m_slow.isnan())).all()

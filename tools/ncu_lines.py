@@ -29,7 +29,8 @@ for l in dis.splitlines():
         continue
     if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
         lines.append(cur_line)
-sel = ["--kernel-id", f"::{kname}:{invocation}"] if invocation else ["--kernel-name", kname]
+nk = os.environ.get("NCU_KNAME", kname)  # template instantiations: mangled name for the cubin, plain for ncu
+sel = ["--kernel-id", f"::{nk}:{invocation}"] if invocation else ["--kernel-name", nk]
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + sel,
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
