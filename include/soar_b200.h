@@ -254,6 +254,72 @@ int soar_post_backward(const SoarPostArgs* args, const float* dL_dout_normal, co
                        const float* dL_ddepth_normal, float* dL_dnormal, float* dL_ddepth,
                        soar_stream_t stream);
 
+/* ---- optimizer step and densify / clone / split / prune of the Gaussian parameter groups
+ *      (replaces torch.optim.Adam over the per-Gaussian groups, TS/geometry/surfel_base.py:596-681,
+ *      and the boolean-mask / torch.cat / optimizer-state surgery of :847-1135) ------------------ */
+#define SOAR_ADAM_MAX_GROUPS 16
+typedef struct SoarAdamGroup {
+  float* param;              /* updated in place                                   */
+  const float* grad;
+  float* exp_avg;            /* Adam first moment, in place                        */
+  float* exp_avg_sq;         /* Adam second moment, in place                       */
+  int64_t numel;
+  double lr;                 /* this group's learning rate for this step           */
+  int32_t step;              /* 1-based step count of this group's state           */
+  int32_t reserved;
+} SoarAdamGroup;
+/* One launch for all groups; torch.optim.Adam semantics (no amsgrad / weight decay). The
+ * hyper-parameters are doubles like torch's python scalars: 1 - beta, the bias corrections and the
+ * step size are formed in double and rounded to float once. */
+int soar_adam_step(const SoarAdamGroup* groups, int32_t n_groups, double beta1, double beta2,
+                   double eps, soar_stream_t stream);
+
+typedef struct SoarDensifyStats {      /* each [N] (the reference keeps [N,1])      */
+  float* xyz_gradient_accum;
+  float* scale_gradient_accum;
+  float* rot_gradient_accum;
+  float* opac_gradient_accum;
+  float* denom;
+  float* max_radii2D;
+} SoarDensifyStats;
+/* add_densification_stats (:1113-1135) with update_filter = radii > 0, plus
+ * max_radii2D = max(max_radii2D, radii) (:1214), for one rendered view. viewspace_grad [N,3],
+ * scaling_grad [N,3], rotation [N,4], opacity [N] (the logit parameter), radii [N]. */
+int soar_densify_add_stats(int32_t N, const float* viewspace_grad, const float* scaling_grad,
+                           const float* rotation, const float* opacity, const int32_t* radii,
+                           const SoarDensifyStats* stats, soar_stream_t stream);
+/* mode 0 = adaptive_densify (:1083-1111): out_a = clone mask (:1038-1046), out_b = split mask
+ * (:987-994); mode 1 = adaptive_prune (:1069-1081): out_a = prune mask. scaling [N,3] (log),
+ * opacity [N] (logit). dense_extent = percent_dense * scene_extent, half_extent = 0.5 * extent,
+ * area_thr = 1e-8 * extent^2 (formed by the caller in double, like the python scalars). */
+int soar_densify_select(int32_t N, int32_t mode, const SoarDensifyStats* stats, const float* scaling,
+                        const float* opacity, float max_grad, float dense_extent, float min_opacity,
+                        float half_extent, float area_thr, uint8_t* out_a, uint8_t* out_b,
+                        soar_stream_t stream);
+/* Ascending list of the rows whose mask byte is non-zero (invert: zero) + their count (device). */
+size_t soar_mask_index_workspace_bytes(int32_t N);
+int soar_mask_to_index(const uint8_t* mask, int32_t N, int32_t invert, int32_t* index_out,
+                       uint32_t* count_out, void* workspace, size_t workspace_bytes,
+                       soar_stream_t stream);
+#define SOAR_ROWS_MAX_TENSORS 32
+typedef struct SoarRowTensor {
+  float* data;               /* row-major [rows, width]; NULL source = zeros       */
+  int32_t width;
+  int32_t reserved;
+} SoarRowTensor;
+/* dst[t][dst_row0 + i, :] = src[t][index[i % n_index], :] for i < n_out and every tensor t, one
+ * launch (index NULL: identity). Prune = gather of the kept rows; clone / split = gather of the
+ * selected rows to the tail, with zero rows (NULL source) for the Adam moments (:905-977). */
+int soar_rows_gather(const SoarRowTensor* src, const SoarRowTensor* dst, int32_t n_tensors,
+                     const int32_t* index, int32_t n_index, int64_t n_out, int64_t dst_row0,
+                     soar_stream_t stream);
+/* densify_and_split's new centres and scales (:996-1010): for i < n_sel * n_rep, j = index[i % n_sel]:
+ * out_xyz[i] = R(normalize(rotation[j])) . samples[i] + xyz[j];
+ * out_scaling[i] = log(exp(scaling[j]) / (0.8 * n_rep)), z = -1e10 when surfel. */
+int soar_densify_split_rows(const float* xyz, const float* scaling, const float* rotation,
+                            const int32_t* index, int32_t n_sel, int32_t n_rep, const float* samples,
+                            int32_t surfel, float* out_xyz, float* out_scaling, soar_stream_t stream);
+
 /* ---- launch accounting / event timing (used by bench.py; no reference analogue:
  *      the reference has an unused CUDA-event Timer, TS/utils/cuda_utils.cu:18-42) --- */
 /* Number of kernels this library has launched in this process. */

@@ -99,6 +99,33 @@ class SoarPostArgs(Structure):
     ]
 
 
+class SoarAdamGroup(Structure):
+    _fields_ = [
+        ("param", c_void_p),
+        ("grad", c_void_p),
+        ("exp_avg", c_void_p),
+        ("exp_avg_sq", c_void_p),
+        ("numel", ctypes.c_int64),
+        ("lr", ctypes.c_double),
+        ("step", c_int32),
+        ("reserved", c_int32),
+    ]
+
+
+class SoarDensifyStats(Structure):
+    _fields_ = [(k, c_void_p) for k in ("xyz_gradient_accum", "scale_gradient_accum",
+                                        "rot_gradient_accum", "opac_gradient_accum", "denom",
+                                        "max_radii2D")]
+
+
+class SoarRowTensor(Structure):
+    _fields_ = [("data", c_void_p), ("width", c_int32), ("reserved", c_int32)]
+
+
+ADAM_MAX_GROUPS = 16
+ROWS_MAX_TENSORS = 32
+
+
 # name -> (restype, argtypes); mirrors include/soar_b200.h one to one
 SIGNATURES = {
     "soar_rast_geom_bytes": (c_size_t, [c_int32]),
@@ -168,6 +195,32 @@ SIGNATURES = {
     "soar_post_backward": (
         c_int32,
         [POINTER(SoarPostArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_adam_step": (c_int32, [POINTER(SoarAdamGroup), c_int32, ctypes.c_double, ctypes.c_double,
+                                ctypes.c_double, c_void_p]),
+    "soar_densify_add_stats": (
+        c_int32,
+        [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(SoarDensifyStats), c_void_p],
+    ),
+    "soar_densify_select": (
+        c_int32,
+        [c_int32, c_int32, POINTER(SoarDensifyStats), c_void_p, c_void_p, c_float, c_float, c_float,
+         c_float, c_float, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_mask_index_workspace_bytes": (c_size_t, [c_int32]),
+    "soar_mask_to_index": (
+        c_int32,
+        [c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "soar_rows_gather": (
+        c_int32,
+        [POINTER(SoarRowTensor), POINTER(SoarRowTensor), c_int32, c_void_p, c_int32, ctypes.c_int64,
+         ctypes.c_int64, c_void_p],
+    ),
+    "soar_densify_split_rows": (
+        c_int32,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p, c_int32, c_void_p,
+         c_void_p, c_void_p],
     ),
     "soar_launch_count": (ctypes.c_ulonglong, []),
     "soar_prof_enable": (None, [c_int32]),

@@ -286,3 +286,37 @@ def avatar_gaussians(N, v_template, seed=0):
     return dict(points=_t(pts), rot=_t(q), colors=_t(rng.uniform(0.0, 1.0, size=(N, 3))),
                 occ=_t(1.0 / (1.0 + np.exp(-rng.normal(size=(N, 1))))),
                 scale_jitter=_t(rng.uniform(0.5, 1.5, size=(N, 1))))
+
+
+def densify_problem(N, R=3, seed=0, n_adam=3, n_views=2):
+    """Per-Gaussian parameter groups as the reference holds them (row f3) plus a scripted sequence of
+    gradients: xyz [N,3], f_dc [N,1,3], f_rest [N,R,3], color [N,3], opacity [N,1] (logit), scaling
+    [N,3] (log, z = -1e10 like the surfels), rotation [N,4]; `adam_grads`: n_adam dicts of gradients;
+    `views`: n_views × (viewspace_grad [N,3], radii [N] int32 with ~30 % culled, scaling_grad [N,3])."""
+    rng = np.random.Generator(np.random.PCG64(seed + 15485863))
+    sc = np.log(np.exp(rng.uniform(math.log(0.002), math.log(0.05), size=(N, 3))))
+    sc[:, 2] = -1e10
+    q = rng.normal(size=(N, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    q *= rng.uniform(0.8, 1.25, size=(N, 1))
+    params = dict(xyz=_t(rng.uniform(-1, 1, size=(N, 3))), f_dc=_t(rng.normal(size=(N, 1, 3))),
+                  f_rest=_t(rng.normal(scale=0.3, size=(N, R, 3))), color=_t(rng.normal(size=(N, 3))),
+                  opacity=_t(rng.normal(loc=-1.0, scale=2.0, size=(N, 1))), scaling=_t(sc), rotation=_t(q))
+    shapes = {k: tuple(v.shape[1:]) for k, v in params.items()}
+
+    def grads(n):
+        g = {k: _t(rng.normal(scale=0.1, size=(n,) + s)) for k, s in shapes.items()}
+        g["scaling"][:, 2] = 0.0
+        return g
+
+    def view(n):
+        radii = rng.integers(1, 40, size=n).astype(np.int32)
+        radii[rng.uniform(size=n) < 0.3] = 0
+        sg = rng.normal(scale=1e-3, size=(n, 3))
+        sg[:, 2] = 0.0
+        return _t(rng.normal(size=(n, 3))), torch.from_numpy(radii), _t(sg)
+
+    return dict(params=params, adam_grads=[grads(N) for _ in range(n_adam)],
+                views=[view(N) for _ in range(n_views)], grads=grads, view=view,
+                lrs=dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, color=2.5e-3, opacity=0.05,
+                         scaling=5e-3, rotation=1e-3))
