@@ -583,6 +583,84 @@ def postops_report(device, W=1024, H=1024, iters=50, cpu=True):
     return out
 
 
+def densify_report(device, N=500_000, R=15, iters=20):
+    """Row f3 stage report at the bench size (500k Gaussians, SH3-sized f_rest): the fused Adam
+    step, the per-view statistics and one prune + clone + split cycle — our launches against the
+    reference's way of doing it (torch.optim.Adam + oracle/densify_oracle.py's torch op chain, which
+    is pinned to the reference's own methods) on the same B200. CUDA events; data resident."""
+    from oracle import densify_oracle as O
+    from soar_b200 import synthetic
+    from soar_b200.densify import GROUPS, GaussianStore
+    pb = synthetic.densify_problem(N, R=R, seed=0, n_adam=1, n_views=1)
+    P = {k: v.to(device) for k, v in pb["params"].items()}
+    G = {k: v.to(device) for k, v in pb["adam_grads"][0].items()}
+    vg, radii, sg = (t.to(device) for t in pb["views"][0])
+    nbytes = sum(v.numel() for v in P.values()) * 4
+
+    def timed(fn, n=iters, setup=None):
+        ts = []
+        for i in range(n + 2):
+            arg = setup() if setup else None
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(device)
+            e0.record()
+            fn(arg) if setup else fn()
+            e1.record()
+            torch.cuda.synchronize(device)
+            if i >= 2:
+                ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        return ts[len(ts) // 2]
+
+    st = GaussianStore(*(P[k] for k in GROUPS))
+    st.training_setup(pb["lrs"])
+    ours_adam = timed(lambda: st.step(G))
+    tp = [torch.nn.Parameter(P[k].clone()) for k in GROUPS]
+    for p_, k in zip(tp, GROUPS):
+        p_.grad = G[k]
+    opt = torch.optim.Adam([{"params": [p_], "lr": pb["lrs"][k]} for p_, k in zip(tp, GROUPS)], lr=0.0, eps=1e-15)
+    ref_adam = timed(opt.step)
+    ours_stats = timed(lambda: st.add_densification_stats(vg, radii, sg))
+    ost = O.new_state(P)
+    ref_stats = timed(lambda: O.add_densification_stats(ost, vg, radii, sg))
+
+    def fresh_store():
+        s_ = GaussianStore(*(P[k] for k in GROUPS))
+        s_.training_setup(pb["lrs"])
+        s_.step(G)
+        s_.add_densification_stats(vg, radii, sg)
+        return s_
+
+    def fresh_state():
+        o_ = O.new_state(P)
+        O.adam_step(o_, G, pb["lrs"])
+        O.add_densification_stats(o_, vg, radii, sg)
+        return o_
+
+    counts = {}
+
+    def ours_cycle(s_):
+        s_.adaptive_prune(0.1, 1.0)
+        counts["clone_split"] = s_.adaptive_densify(0.8, 1.0)
+        counts["n_after"] = s_.num_points
+
+    def ref_cycle(o_):
+        O.adaptive_prune(o_, 0.1, 1.0)
+        _, split = O.densify_masks(o_, 0.8, 1.0)
+        stds = torch.exp(o_["p"]["scaling"])[split].repeat(2, 1)
+        O.adaptive_densify(o_, 0.8, 1.0, torch.normal(torch.zeros_like(stds), stds))
+
+    ours_cyc = timed(ours_cycle, n=5, setup=fresh_store)
+    ref_cyc = timed(ref_cycle, n=5, setup=fresh_state)
+    return {"workload": f"f3: {N} Gaussians, f_rest [{N},{R},3]: Adam step over the 7 groups, per-view statistics, "
+                        "prune + clone + split cycle",
+            "adam_ms": ours_adam, "adam_torch_same_gpu_ms": ref_adam,
+            "adam_GBps": nbytes * 7 / (ours_adam * 1e-3) / 1e9,   # p, g, m, v read + p, m, v written
+            "stats_ms": ours_stats, "stats_torch_same_gpu_ms": ref_stats,
+            "densify_cycle_ms": ours_cyc, "densify_cycle_torch_same_gpu_ms": ref_cyc,
+            "densify_counts": counts}
+
+
 def c5_report(device, N=2_000_000, W=1920, H=1080, iters=5):
     """BASELINE config 5 on one GPU (a parity-test configuration, reported for scale): one
     dance_0-shaped step — SMPL-X pose, 30-NN skin-weight query, skinning, surfel rasterizer pass +
@@ -727,9 +805,10 @@ def main():
     if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
         post = postops_report(device, wl.W, wl.H, cpu=not args.no_cpu_baseline)
 
-    c5 = None
+    c5 = dens = None
     if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
         c5 = c5_report(device)
+        dens = densify_report(device)
 
     if rank == 0:
         line = {
@@ -748,7 +827,7 @@ def main():
                        "P_visible": Pv, "num_rendered": R,
                        "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
             "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,
-            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post, "c5_step": c5,
+            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post, "c5_step": c5, "densify": dens,
         }
         if args.impl == "reference":
             line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
