@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(SORT_RADIX) radix_hist_scan_kernel(uint32_t* g
 }
 
 // vals_in == nullptr: the value of element i is i (first pass of the depth sort).
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, 4)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                       const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
                       uint32_t n, int shift, int nbits, uint32_t flip,
@@ -518,6 +518,10 @@ int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int en
   SOAR_CUDA_TRY(cudaFuncSetAttribute(radix_onesweep_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)SORT_SMEM_BYTES));
+  // 4 CTAs/SM (64 registers under the launch bound) need 4 x 35 KB of shared memory
+  SOAR_CUDA_TRY(cudaFuncSetAttribute(radix_onesweep_kernel,
+                                     cudaFuncAttributePreferredSharedMemoryCarveout,
+                                     cudaSharedmemCarveoutMaxShared));
   for (int p = 0; p < passes; ++p) {
     const int shift = p * SORT_RADIX_BITS;
     const int bits = min(SORT_RADIX_BITS, end_bit - shift);
