@@ -435,7 +435,7 @@ def profile_pass(arm, wl, steps):
     lib.soar_prof_enable(1)
     for s in range(steps):
         step_resident(arm, wl, 1000 + s)
-    n = 32
+    n = 256  # >= the library's kernel-id count (soar_prof_summary fills at most this many)
     counts = (ctypes.c_int32 * n)()
     ms = (ctypes.c_float * n)()
     k = lib.soar_prof_summary(n, counts, ms)
@@ -558,7 +558,7 @@ def postops_report(device, W=1024, H=1024, iters=50, cpu=True):
     lib.soar_prof_enable(1)
     for _ in range(iters):
         run(postops.surfel_postprocess, dev)
-    n = 32
+    n = 256  # >= the library's kernel-id count (soar_prof_summary fills at most this many)
     counts, ms = (ctypes.c_int32 * n)(), (ctypes.c_float * n)()
     k = lib.soar_prof_summary(n, counts, ms)
     kern = {lib.soar_kernel_name(i).decode(): ms[i] / counts[i] for i in range(k) if counts[i]}
@@ -711,7 +711,7 @@ def c5_report(device, N=2_000_000, W=1920, H=1080, iters=5):
         step()
     e1.record()
     torch.cuda.synchronize(device)
-    n = 32
+    n = 256  # >= the library's kernel-id count (soar_prof_summary fills at most this many)
     counts, ms = (ctypes.c_int32 * n)(), (ctypes.c_float * n)()
     k = lib.soar_prof_summary(n, counts, ms)
     kern = {lib.soar_kernel_name(i).decode(): round(ms[i] / iters, 4) for i in range(k) if counts[i]}

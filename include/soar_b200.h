@@ -320,6 +320,27 @@ int soar_densify_split_rows(const float* xyz, const float* scaling, const float*
                             const int32_t* index, int32_t n_sel, int32_t n_rep, const float* samples,
                             int32_t surfel, float* out_xyz, float* out_scaling, soar_stream_t stream);
 
+/* ---- the reachable kernels of the reference's `cuda_utils` extension ----- */
+/* gaussian2occgrid (TS/utils/cuda_utils.cu:779-872, pybind glue TS/utils/ext.cpp:201-255, caller
+ * TS/geometry/surfel_base.py:1150-1195): grid[gx,gy,gz] is zeroed and every surfel adds
+ * alpha = exp(-(dx^2+dy^2)/2) * opac to the cells its disc crosses. pos_min[3], pos_max[3], grid_len[1],
+ * cutoff[1] are DEVICE scalars/vectors like the reference's tensors; grid_dim_host[3] is read on the
+ * host (the reference calls .item() on it to size the grid, ext.cpp:214-216). pos[n,3], rot[n,4]
+ * (w,x,y,z, used un-normalised), scale[n,3] (columns 0,1 used), opac[n]. error_flag (device u32) is
+ * set to 1 when a Gaussian's sample lattice runs for more than 65536 in-bounds steps on an axis (a
+ * grid_len that does not match the bounds: the reference would not return in reasonable time); such
+ * Gaussians are skipped. One launch + two fills. */
+int soar_occgrid_splat(int32_t n, const float* pos_min, const float* pos_max, const float* grid_len,
+                       const float* cutoff, const int32_t* grid_dim_host, const float* pos,
+                       const float* rot, const float* scale, const float* opac, float* grid,
+                       uint32_t* error_flag, soar_stream_t stream);
+/* contour_padding (TS/utils/cuda_utils.cu:226-300, glue TS/utils/ext.cpp:74-107, caller
+ * TS/utils/image_utils.py:317): res[C,H,W] = 0, then every pixel outside mask[H,W] (bool bytes) takes
+ * the mean over the masked pixels of its (2*size+1)^2 window. The reference's indexing is kept: only
+ * plane 0 of res is written, from image[C*(min(15,C)-1) + pixel]. size == 0 returns the zeros. */
+int soar_contour_padding(const float* image, const uint8_t* mask, int32_t C, int32_t H, int32_t W,
+                         int32_t size, float* res, soar_stream_t stream);
+
 /* ---- launch accounting / event timing (used by bench.py; no reference analogue:
  *      the reference has an unused CUDA-event Timer, TS/utils/cuda_utils.cu:18-42) --- */
 /* Number of kernels this library has launched in this process. */

@@ -196,6 +196,15 @@ SIGNATURES = {
         c_int32,
         [POINTER(SoarPostArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "soar_occgrid_splat": (
+        c_int32,
+        [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_int32), c_void_p, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "soar_contour_padding": (
+        c_int32,
+        [c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_void_p, c_void_p],
+    ),
     "soar_adam_step": (c_int32, [POINTER(SoarAdamGroup), c_int32, ctypes.c_double, ctypes.c_double,
                                 ctypes.c_double, c_void_p]),
     "soar_densify_add_stats": (

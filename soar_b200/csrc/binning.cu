@@ -221,8 +221,8 @@ duplicate_tiles_kernel(int P, const float* __restrict__ records, const uint32_t*
       values[slot] = o_idx;
       const uint32_t kf = tile ^ flip;
       for (int p = 0; p < passes; ++p) {
-        const int shift = p * SORT_RADIX_BITS;
-        const int bits = min(SORT_RADIX_BITS, end_bit - shift);
+        const int shift = sort_pass_shift(p, end_bit, passes);
+        const int bits = sort_pass_bits(p, end_bit, passes);
         atomicAdd(&s_hist[p * SORT_RADIX + ((kf >> shift) & ((1u << bits) - 1u))], 1u);
       }
     }
@@ -270,7 +270,7 @@ __constant__ int g_probe;
 #endif
 constexpr int RS_LB = 8;  // look-back words in flight per step
 constexpr size_t SORT_SMEM_BYTES =
-    (2 * (size_t)SORT_TILE + (SORT_THREADS / 32) * SORT_RADIX + 2 * SORT_RADIX + SORT_THREADS / 32 + 4) * 4;
+    (2 * (size_t)SORT_TILE + (SORT_THREADS / 32) * SORT_RADIX + 2 * SORT_RADIX + 2 * (SORT_THREADS / 32) + 4) * 4;
 
 // One pass over the keys builds the digit histograms of every pass.
 __global__ void __launch_bounds__(256)
@@ -283,8 +283,8 @@ radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int passes, int
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const uint32_t k = keys[i] ^ flip;
     for (int p = 0; p < passes; ++p) {
-      const int shift = p * SORT_RADIX_BITS;
-      const int bits = min(SORT_RADIX_BITS, end_bit - shift);
+      const int shift = sort_pass_shift(p, end_bit, passes);
+      const int bits = sort_pass_bits(p, end_bit, passes);
       const uint32_t d = (k >> shift) & ((1u << bits) - 1u);
       atomicAdd(&sh[p * SORT_RADIX + d], 1u);
     }
@@ -296,32 +296,36 @@ radix_hist_kernel(const uint32_t* __restrict__ keys, uint32_t n, int passes, int
   }
 }
 
-// ghist[p][d] -> exclusive prefix over d, one CTA per pass.
-__global__ void __launch_bounds__(SORT_RADIX) radix_hist_scan_kernel(uint32_t* ghist) {
-  __shared__ uint32_t s_warp[SORT_RADIX / 32];
-  uint32_t* h = ghist + blockIdx.x * SORT_RADIX;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t c = h[tid];
-  uint32_t incl = c;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += t;
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
-  uint32_t off = 0;
-  for (int w = 0; w < warp; ++w) off += s_warp[w];
-  h[tid] = off + incl - c;
+// peers & (lanes whose digit has the same value in the bit `mask` as mine): bit test with a
+// predicate result, ballot, select, one three-input logic op — four instructions per digit bit
+// (the C++ spelling compiles to six).
+__device__ __forceinline__ uint32_t peers_with_same_bit(uint32_t peers, uint32_t d, uint32_t mask) {
+  uint32_t out;
+  asm volatile(
+      "{\n"
+      " .reg .pred p;\n"
+      " .reg .b32 t, bal, m;\n"
+      " and.b32 t, %2, %3;\n"
+      " setp.ne.u32 p, t, 0;\n"
+      " vote.sync.ballot.b32 bal, p, 0xffffffff;\n"
+      " selp.b32 m, 0, 0xffffffff, p;\n"
+      " lop3.b32 %0, %1, bal, m, 0x60;\n"
+      "}"
+      : "=r"(out)
+      : "r"(peers), "r"(d), "r"(mask));
+  return out;
 }
 
 // vals_in == nullptr: the value of element i is i (first pass of the depth sort).
+// NBITS = digit width known at compile time (the ranking loop is then exactly NBITS ballots with no
+// per-bit branch); launch_radix_sort picks the instantiation.
+template <int NBITS>
 __global__ void __launch_bounds__(SORT_THREADS, 4)
 radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict__ keys_out,
                       const uint32_t* __restrict__ vals_in, uint32_t* __restrict__ vals_out,
-                      uint32_t n, int shift, int nbits, uint32_t flip,
-                      const uint32_t* __restrict__ ghist_excl, uint32_t* status, uint32_t* ticket) {
-  const uint32_t digit_mask = (1u << nbits) - 1u;
+                      uint32_t n, int shift, uint32_t flip,
+                      const uint32_t* __restrict__ ghist_count, uint32_t* status, uint32_t* ticket) {
+  constexpr uint32_t digit_mask = (1u << NBITS) - 1u;
   // dynamic shared memory (> 48 KB): keys | vals | per-warp digit histograms | offsets
   extern __shared__ uint32_t s_dyn[];
   uint32_t* const s_keys = s_dyn;
@@ -331,7 +335,8 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
   uint32_t* const s_gofs = s_vals + SORT_TILE + (SORT_THREADS / 32) * SORT_RADIX;
   uint32_t* const s_digit_excl = s_gofs + SORT_RADIX;
   uint32_t* const s_scan = s_digit_excl + SORT_RADIX;
-  uint32_t& s_tile = s_scan[SORT_THREADS / 32];
+  uint32_t* const s_gscan = s_scan + SORT_THREADS / 32;
+  uint32_t& s_tile = s_gscan[SORT_THREADS / 32];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr int NWARPS = SORT_THREADS / 32;
@@ -360,7 +365,7 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
     val[j] = tile_base + local;
     if (vals_in != nullptr && local < n_valid) val[j] = vals_in[tile_base + local];
   }
-  const uint32_t my_ghist = ghist_excl[tid];  // digit tid (SORT_THREADS == SORT_RADIX)
+  const uint32_t my_gcount = ghist_count[tid];  // digit tid (SORT_THREADS == SORT_RADIX)
   const uint32_t lt_mask = lanemask_lt();
   // Rank of a key among the warp's keys with the same digit = (count in earlier items) + (lanes
   // below in this item). The per-digit running count lives in shared memory; the first lane of
@@ -375,12 +380,8 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
     // serialises over the distinct values in the warp)
     uint32_t peers = 0xffffffffu;
 #pragma unroll
-    for (int b = 0; b < SORT_RADIX_BITS; ++b) {
-      if (b < nbits) {  // uniform: short last digits (e.g. 5 tile bits) cost 5 ballots
-        const bool bit = (d >> b) & 1u;
-        const uint32_t bal = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? bal : ~bal;
-      }
+    for (int b = 0; b < NBITS; ++b) {
+      peers = peers_with_same_bit(peers, d, 1u << b);
     }
     const uint32_t lt = __popc(peers & lt_mask);
     const int leader = __ffs(peers) - 1;
@@ -402,28 +403,36 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
       running += t;
     }
     const uint32_t total = running;
+    // digits beyond the pass's width never occur: nothing to publish or to look back over
+    const bool live_digit = d < (1 << NBITS);
     uint32_t* my_status = status + (size_t)tile * SORT_RADIX + d;
-    if (tile == 0) st_relaxed_u32(my_status, RS_FLAG_INCL | total);
-    else st_relaxed_u32(my_status, RS_FLAG_AGG | total);
+    if (live_digit) {
+      if (tile == 0) st_relaxed_u32(my_status, RS_FLAG_INCL | total);
+      else st_relaxed_u32(my_status, RS_FLAG_AGG | total);
+    }
 
-    // block exclusive scan of `total` over digits
-    uint32_t incl = total;
+    // block exclusive scans over digits of `total` (tile-local digit offsets) and of the global
+    // digit counts (where each digit's output region starts; every CTA redoes this 256-entry scan
+    // rather than paying a separate launch per sort for it)
+    uint32_t incl = total, gincl = my_gcount;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += t;
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      const uint32_t g = __shfl_up_sync(0xffffffffu, gincl, o);
+      if (lane >= o) { incl += t; gincl += g; }
     }
-    if (lane == 31) s_scan[warp] = incl;
+    if (lane == 31) { s_scan[warp] = incl; s_gscan[warp] = gincl; }
     __syncthreads();
-    uint32_t off = 0;
-    for (int w = 0; w < warp; ++w) off += s_scan[w];
+    uint32_t off = 0, goff = 0;
+    for (int w = 0; w < warp; ++w) { off += s_scan[w]; goff += s_gscan[w]; }
     const uint32_t digit_excl = off + incl - total;
+    const uint32_t my_ghist = goff + gincl - my_gcount;
     s_digit_excl[d] = digit_excl;
 
     // decoupled look-back over predecessor tiles for this digit; RS_LB status words are
     // fetched per step so the chain costs one L2 round trip per RS_LB tiles, not per tile
     uint32_t prev = 0;
-    if (tile != 0 && !SORT_PROBE(0)) {
+    if (tile != 0 && live_digit && !SORT_PROBE(0)) {
       int t = (int)tile - 1;
       bool found = false;
       while (!found) {
@@ -477,10 +486,26 @@ radix_onesweep_kernel(const uint32_t* __restrict__ keys_in, uint32_t* __restrict
   }
 }
 
+typedef void (*OnesweepFn)(const uint32_t*, uint32_t*, const uint32_t*, uint32_t*, uint32_t, int,
+                           uint32_t, const uint32_t*, uint32_t*, uint32_t*);
+static OnesweepFn onesweep_for_bits(int bits) {
+  switch (bits) {
+    case 1: return radix_onesweep_kernel<1>;
+    case 2: return radix_onesweep_kernel<2>;
+    case 3: return radix_onesweep_kernel<3>;
+    case 4: return radix_onesweep_kernel<4>;
+    case 5: return radix_onesweep_kernel<5>;
+    case 6: return radix_onesweep_kernel<6>;
+    case 7: return radix_onesweep_kernel<7>;
+    default: return radix_onesweep_kernel<8>;
+  }
+}
+
 // Stable sort of `n` (u32 key, u32 value) pairs by key bits [0, end_bit). Input in
 // keys[0]/values[0] (values[0] may be implied = element index when iota_values);
 // *result_buf = index (0/1) of the buffer pair holding the result.
-// `ghist` (passes*256 u32) must hold the digit COUNTS when have_hist, else zeros;
+// `ghist` (passes*256 u32) must hold the digit COUNTS when have_hist, else zeros (it keeps the counts:
+// the passes scan them themselves);
 // `status` must be zero on entry.
 int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int end_bit,
                       bool descending, bool iota_values, bool have_hist, uint32_t* ghist,
@@ -508,28 +533,23 @@ int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int en
     radix_hist_kernel<<<hist_blocks, 256, 0, stream>>>(keys[0], n, passes, end_bit, flip, ghist);
   }
   SOAR_LAUNCH_CHECK("radix_hist_kernel");
-  {
-    KernelScope ks(K_RADIX_HIST_SCAN, stream);
-    radix_hist_scan_kernel<<<passes, SORT_RADIX, 0, stream>>>(ghist);
-  }
-  SOAR_LAUNCH_CHECK("radix_hist_scan_kernel");
   uint32_t* tickets = status + (size_t)passes * n_sort_tiles * SORT_RADIX;
   // per device and idempotent (a host-side attribute write, no device work)
-  SOAR_CUDA_TRY(cudaFuncSetAttribute(radix_onesweep_kernel,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)SORT_SMEM_BYTES));
-  // 4 CTAs/SM (64 registers under the launch bound) need 4 x 35 KB of shared memory
-  SOAR_CUDA_TRY(cudaFuncSetAttribute(radix_onesweep_kernel,
-                                     cudaFuncAttributePreferredSharedMemoryCarveout,
-                                     cudaSharedmemCarveoutMaxShared));
   for (int p = 0; p < passes; ++p) {
-    const int shift = p * SORT_RADIX_BITS;
-    const int bits = min(SORT_RADIX_BITS, end_bit - shift);
+    const int shift = sort_pass_shift(p, end_bit, passes);
+    const int bits = sort_pass_bits(p, end_bit, passes);
+    OnesweepFn fn = onesweep_for_bits(bits);
+    // per device and idempotent (host-side attribute writes, no device work); 4 CTAs/SM (64
+    // registers under the launch bound) need 4 x 35 KB of shared memory
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)SORT_SMEM_BYTES));
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                       cudaSharedmemCarveoutMaxShared));
     {
       KernelScope ks(K_RADIX_ONESWEEP, stream);
-      radix_onesweep_kernel<<<tiles, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
+      fn<<<tiles, SORT_THREADS, SORT_SMEM_BYTES, stream>>>(
           keys[p & 1], keys[(p + 1) & 1], (p == 0 && iota_values) ? nullptr : values[p & 1],
-          values[(p + 1) & 1], n, shift, bits, flip, ghist + p * SORT_RADIX,
+          values[(p + 1) & 1], n, shift, flip, ghist + p * SORT_RADIX,
           status + (size_t)p * n_sort_tiles * SORT_RADIX, tickets + p);
     }
     SOAR_LAUNCH_CHECK("radix_onesweep_kernel");

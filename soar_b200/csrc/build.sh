@@ -10,7 +10,7 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-O3 -std=c++17 -Xcompiler -fPIC -gencode arch=compute_100a,code=sm_100a -lineinfo ${SOAR_NVCC_EXTRA:-}"
 mkdir -p "$OBJ"
 pids=()
-for f in api prof preprocess binning blend_fwd blend_bwd geom_bwd knn lbs lbs_query smplx postops densify; do
+for f in api prof preprocess binning blend_fwd blend_bwd geom_bwd knn lbs lbs_query smplx postops densify occgrid; do
   src="$HERE/$f.cu"; obj="$OBJ/$f.o"
   newest=$(ls -t "$src" "$HERE"/*.h "$HERE"/*.cuh "$HERE/../../include/soar_b200.h" | head -1)
   if [ ! -f "$obj" ] || [ "$newest" -nt "$obj" ]; then

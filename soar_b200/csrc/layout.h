@@ -41,6 +41,18 @@ constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 4;    // 32-bit keys
 constexpr int SORT_MAX_PASSES_R = 4;  // tile-id sort (up to 32 tile bits)
 inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
+// The key bits are spread evenly over the passes (12 tile bits sort as 6+6, not 8+4): the same number
+// of ballots in total, but fewer digits to publish / look back over and longer scatter runs per digit.
+__host__ __device__ inline int sort_bits_per_pass(int end_bit, int passes) {
+  return passes > 0 ? (end_bit + passes - 1) / passes : 0;
+}
+__host__ __device__ inline int sort_pass_shift(int p, int end_bit, int passes) {
+  return p * sort_bits_per_pass(end_bit, passes);
+}
+__host__ __device__ inline int sort_pass_bits(int p, int end_bit, int passes) {
+  const int per = sort_bits_per_pass(end_bit, passes), left = end_bit - p * per;
+  return left < per ? left : per;
+}
 
 struct GeomLayout {
   size_t records;        // float[P*24]
