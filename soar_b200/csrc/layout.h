@@ -36,6 +36,11 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 12;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;  // 3072 pairs per CTA
+// One tile size for every input: 1024-pair tiles for the small sorts (the depth sort of P = 500k
+// Gaussians) were measured slower on the B200 (58 vs 50 us for the four passes, tools/sort_probe.cu):
+// three times the tiles make the look-back chain and the status traffic longer than the shorter
+// per-CTA work saves.
+inline int sort_tiles_for(size_t n) { return (int)((n + SORT_TILE - 1) / SORT_TILE); }
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 4;    // 32-bit keys
@@ -83,7 +88,7 @@ inline GeomLayout geom_layout(size_t P) {
   L.scan_status_bytes = align_up(n_tiles * sizeof(uint64_t) + 16, 256);
   off += L.scan_status_bytes;
   L.ghist = off;          off = align_up(off + SORT_MAX_PASSES * SORT_RADIX * 4, 256);
-  L.n_sort_tiles = (int)((P + SORT_TILE - 1) / SORT_TILE);
+  L.n_sort_tiles = sort_tiles_for(P);
   L.sort_status = off;
   off = align_up(off + ((size_t)SORT_MAX_PASSES * L.n_sort_tiles * SORT_RADIX + SORT_MAX_PASSES) * 4, 256);
   L.zero_bytes = off - L.zero_begin;
@@ -131,7 +136,7 @@ inline BinningLayout binning_layout(size_t R, int passes) {
   L.keys[1] = off;   off = align_up(off + R * 4, 256);
   L.values[0] = off; off = align_up(off + R * 4, 256);
   L.values[1] = off; off = align_up(off + R * 4, 256);
-  L.n_sort_tiles = (int)((R + SORT_TILE - 1) / SORT_TILE);
+  L.n_sort_tiles = sort_tiles_for(R);
   L.zero_begin = off;
   L.ghist = off;     off = align_up(off + SORT_MAX_PASSES_R * SORT_RADIX * 4, 256);
   L.status = off;

@@ -22,7 +22,7 @@ int main(int argc, char** argv) {
   uint32_t *k[2], *v[2];
   for (int i = 0; i < 2; ++i) { cudaMalloc(&k[i], n * 4); cudaMalloc(&v[i], n * 4); }
   const int passes = sort_passes(bits);
-  const int tiles = (n + SORT_TILE - 1) / SORT_TILE;
+  const int tiles = sort_tiles_for(n);
   uint32_t *ghist, *status;
   cudaMalloc(&ghist, 4 * 256 * 4);
   const size_t status_bytes = ((size_t)passes * tiles * 256 + 8) * 4;
