@@ -43,14 +43,31 @@ __device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
 // 128 threads x 4 CTAs/SM under a 128-register cap (16 B of spill): twice the loads in flight of
 // the uncapped 154-register build, which ran one 256-thread CTA per SM and stalled on the long scoreboard.
 constexpr int GB_THREADS = 128;
+// (Requesting the CTA's row blocks with prefetch.global.L2 up front was measured: 125 vs 114 us —
+// the extra requests compete with the demand loads; not done.)
 template <bool LRN_CAM, int SHV>
-__global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdArgs a) {
-  // config lives on the device: both variants are launched, the one that does
-  // not match config[3] (lrn_cam) retires immediately.
-  if ((a.config[3] > 0) != LRN_CAM) return;
+__device__ __forceinline__ void geom_bwd_body(const GeomBwdArgs& a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const bool in_range = idx < a.P;
-  const bool visible = in_range && a.radii[idx] > 0;
+  // Everything that depends on idx alone is requested before the visibility test is known, so
+  // the radius, the accumulator, the record and the parameters share one DRAM round trip
+  // (culled Gaussians, ~6 %, fetch them for nothing).
+  float4 A0 = make_float4(0.f, 0.f, 0.f, 0.f), A1 = A0, A2 = A0, A3 = A0, r0 = A0, r1 = A0;
+  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  float3 mean_in = make_float3(0.f, 0.f, 0.f), scale_in = make_float3(0.f, 0.f, 0.f);
+  int radius = 0;
+  if (in_range) {
+    radius = a.radii[idx];
+    const float4* acc4 = reinterpret_cast<const float4*>(a.gacc + (size_t)idx * GACC_FLOATS);
+    A0 = acc4[0]; A1 = acc4[1]; A2 = acc4[2]; A3 = acc4[3];
+    const float4* rec = reinterpret_cast<const float4*>(a.records + (size_t)idx * REC_FLOATS);
+    r0 = __ldg(rec + 0); r1 = __ldg(rec + 1);
+    mean_in = make_float3(a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]);
+    if (a.rotations != nullptr) q_in = reinterpret_cast<const float4*>(a.rotations)[idx];
+    if (a.scales != nullptr)
+      scale_in = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
+  }
+  const bool visible = in_range && radius > 0;
   const uint32_t accm = a.g.accumulate_mask;
   const bool acc_m2d = accm & SOAR_ACC_MEANS2D, acc_col = accm & SOAR_ACC_COLORS,
              acc_opa = accm & SOAR_ACC_OPACITY, acc_m3d = accm & SOAR_ACC_MEANS3D,
@@ -96,8 +113,6 @@ __global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdAr
     const bool surface = a.config[0] > 0;
     // accumulator (layout.h GaccSlot): dcolor[3] ddepth dopacity | six dL/ddist moments |
     // dnormal[3] and the per-pixel-depth sum
-    const float4* acc4 = reinterpret_cast<const float4*>(a.gacc + (size_t)idx * GACC_FLOATS);
-    const float4 A0 = acc4[0], A1 = acc4[1], A2 = acc4[2], A3 = acc4[3];
     const float dL_dcolor[3] = {A0.x, A0.y, A0.z};
     const float dL_ddepth = A0.w;
     const float dL_dopac = A1.x;
@@ -106,7 +121,6 @@ __global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdAr
     // dL/dmean2D (NDC-scaled, Q10) and dL/dconic from the moments (backward.cu:820-855), with the
     // conic the blend kernels used (the forward's record)
     const float4* rec = reinterpret_cast<const float4*>(a.records + (size_t)idx * REC_FLOATS);
-    const float4 r0 = __ldg(rec + 0), r1 = __ldg(rec + 1);
     const float cA = r0.z, cB = r0.w, cC = r1.x;
     const float ddelx_dx = 0.5 * a.W;
     const float ddely_dy = 0.5 * a.H;
@@ -128,16 +142,11 @@ __global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdAr
       put(a.g.dL_dopacity + idx, dL_dopac, acc_opa);
     }
 
-    const float3 mean = {a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]};
+    const float3 mean = mean_in;
     Mat3 R = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
-    float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
-    if (a.rotations != nullptr) {
-      q = reinterpret_cast<const float4*>(a.rotations)[idx];
-      R = quat_to_rot(q.x, q.y, q.z, q.w);
-    }
-    float3 scale = {0.f, 0.f, 0.f};
-    if (a.scales != nullptr)
-      scale = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
+    const float4 q = q_in;
+    if (a.rotations != nullptr) R = quat_to_rot(q.x, q.y, q.z, q.w);
+    const float3 scale = scale_in;
 
     // ---- cov3D as the forward produced it ----------------------------------------
     float cov3D[6];
@@ -505,6 +514,14 @@ __global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdAr
   }
 }
 
+// config lives on the device (the reference passes a float tensor): one kernel, the lrn_cam body
+// selected by a uniform branch (a second launch that retires immediately still costs ~6 us).
+template <int SHV>
+__global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdArgs a) {
+  if (a.config[3] > 0) geom_bwd_body<true, SHV>(a);
+  else geom_bwd_body<false, SHV>(a);
+}
+
 int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
   // camera gradients are sums: clear them here (the reference gets zeros from torch)
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dviewmat, 0, 16 * sizeof(float), stream));
@@ -517,15 +534,9 @@ int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
   const int shv = (aligned && a.M == 16) ? 16 : (aligned && a.M == 4 ? 4 : 0);
   {
     KernelScope ks(K_GEOM_BWD, stream);
-    if (shv == 16) geom_bwd_kernel<false, 16><<<grid, GB_THREADS, 0, stream>>>(a);
-    else if (shv == 4) geom_bwd_kernel<false, 4><<<grid, GB_THREADS, 0, stream>>>(a);
-    else geom_bwd_kernel<false, 0><<<grid, GB_THREADS, 0, stream>>>(a);
-  }
-  {
-    KernelScope ks(K_GEOM_BWD, stream);
-    if (shv == 16) geom_bwd_kernel<true, 16><<<grid, GB_THREADS, 0, stream>>>(a);
-    else if (shv == 4) geom_bwd_kernel<true, 4><<<grid, GB_THREADS, 0, stream>>>(a);
-    else geom_bwd_kernel<true, 0><<<grid, GB_THREADS, 0, stream>>>(a);
+    if (shv == 16) geom_bwd_kernel<16><<<grid, GB_THREADS, 0, stream>>>(a);
+    else if (shv == 4) geom_bwd_kernel<4><<<grid, GB_THREADS, 0, stream>>>(a);
+    else geom_bwd_kernel<0><<<grid, GB_THREADS, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("geom_bwd_kernel");
   return SOAR_OK;
