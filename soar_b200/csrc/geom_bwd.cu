@@ -29,6 +29,7 @@ __device__ __forceinline__ void warp_atomic_add(float* dst, float v) {
 // what the caller's buffer already holds (multi-view steps accumulate every view straight into the
 // flat all-reduce buffer instead of going through a separate add kernel per tensor per view) and
 // culled Gaussians write nothing at all.
+#ifdef SOAR_GEOM_RMW
 __device__ __forceinline__ void put(float* p, float v, bool acc) { *p = acc ? *p + v : v; }
 __device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
   if (acc) {
@@ -37,6 +38,19 @@ __device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
   }
   *p = v;
 }
+#else
+// Accumulation is a fire-and-forget reduction at the L2 (red.global.add, 16 bytes at a time): the
+// same single rounding as load + add + store, without the DRAM round trip of the load at the tail of
+// every thread. One add per element and launch, launches ordered by the stream: deterministic.
+__device__ __forceinline__ void put(float* p, float v, bool acc) {
+  if (acc) atomicAdd(p, v);
+  else *p = v;
+}
+__device__ __forceinline__ void put4(float4* p, float4 v, bool acc) {
+  if (acc) atomicAdd(p, v);
+  else *p = v;
+}
+#endif
 
 // SHV: SH coefficients per Gaussian moved with 16-byte loads/stores (16 or 4; rows are then
 // 192 / 48 bytes, 16-byte aligned); 0 = generic scalar path for any M.
