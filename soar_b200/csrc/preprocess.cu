@@ -34,6 +34,14 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
   const float* __restrict__ proj = a.projmatrix;
 
   float3 p_orig = {a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]};
+  // the other small per-Gaussian inputs are requested together with the mean, ahead of the culling
+  // tests that decide whether they are needed: one DRAM round trip instead of three
+  float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
+  if (a.rotations != nullptr) q_in = reinterpret_cast<const float4*>(a.rotations)[idx];
+  float3 sc_in = make_float3(0.f, 0.f, 0.f);
+  if (a.cov3D_precomp == nullptr)
+    sc_in = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
+  const float opac_in = a.opacities[idx];
   float4 p_hom = xform_point_4x4(p_orig, proj);
   float p_w = 1.0f / (p_hom.w + 0.0000001f);
   float3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
@@ -55,10 +63,7 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
   }
 
   Mat3 R = mat3_cols(1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f);
-  if (a.rotations != nullptr) {
-    const float4 q = reinterpret_cast<const float4*>(a.rotations)[idx];
-    R = quat_to_rot(q.x, q.y, q.z, q.w);
-  }
+  if (a.rotations != nullptr) R = quat_to_rot(q_in.x, q_in.y, q_in.z, q_in.w);
 
   const bool surface = a.config[0] > 0, pix_depth = a.config[2] > 0;
   float3 n_view = {0.f, 0.f, 0.f};
@@ -88,7 +93,7 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
   if (a.cov3D_precomp != nullptr) {
     cov3D = a.cov3D_precomp + idx * 6;
   } else {
-    float3 sc = {a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]};
+    const float3 sc = sc_in;
     scale_rot_to_cov3d(sc, a.scale_modifier, R, surface, cov3D_local);
     cov3D = cov3D_local;
   }
@@ -142,7 +147,7 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
   // "power < REC_THR" proves alpha < 1/255 without evaluating expf; anything else still takes
   // the reference's exact test. o <= 0 (or NaN) never contributes: +inf rejects every pixel
   // only when the exact test would too, so keep such Gaussians on the exact path with -inf.
-  const float opac = a.opacities[idx];
+  const float opac = opac_in;
   float thr = -INFINITY;
   if (opac > 0.f && opac < INFINITY) thr = -logf(255.0f * opac) - 0.02f;
 
