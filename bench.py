@@ -9,9 +9,11 @@ buffer when N > 1 (weak scaling: per-GPU work fixed). value = frames of all rank
 device time.
 
   value   inputs (Gaussians, cameras, cotangents) resident in HBM; CUDA events around K steps.
-  e2e     the same frames through the public API (GaussianRasterizer + autograd), with this
+  e2e     the same frames through the public API (GaussianRasterizer + autograd), with every
           step's cameras and target images copied host->device from pinned memory inside the
-          timed region, an L2 loss on the four outputs, and the loss scalar read back.
+          timed region (double buffered one view ahead, across step boundaries too), an L2 loss
+          on the four outputs (loss_and_cotangents: the same torch launches for both arms), and the
+          loss scalar read back every step.
   roofline   dominant kernel by event time (soar_prof_* in the C-ABI library), algorithmic bytes
              from DESIGN.md / SURVEY.md §8d with the measured R, Pv.
   cpu_baseline  the CPU restatement of the rasterizer (oracle/, C + OpenMP) timed on the host cores
@@ -158,8 +160,11 @@ class Workload:
         self.copy_stream = torch.cuda.Stream(device=device)
         self.copied = [torch.cuda.Event() for _ in range(2)]
         self.consumed = [torch.cuda.Event() for _ in range(2)]
-        self.cam_all = [torch.empty(35, **f32) for _ in range(views_per_rank)]
-        self.cams_copied, self.cams_consumed = torch.cuda.Event(), torch.cuda.Event()
+        # cameras of a step, double buffered over steps (the next step's are prefetched)
+        self.cam_all = [[torch.empty(35, **f32) for _ in range(views_per_rank)] for _ in range(2)]
+        self.cams_copied = [torch.cuda.Event() for _ in range(2)]
+        self.cams_consumed = [torch.cuda.Event() for _ in range(2)]
+        self.prefetched = None  # step whose first inputs are already on their way
         self.loss_host = torch.zeros(1).pin_memory()
 
     def scene_dict(self, cam_flat):
@@ -180,6 +185,19 @@ class Workload:
 
     def h2d_bytes_per_step(self):
         return self.vpr * (35 * 4 + 8 * self.H * self.W * 4)
+
+
+def loss_and_cotangents(color, normal, depth, opac, tgt):
+    """The e2e step's loss — sum of the four mean squared errors against the 8-channel target — and
+    its gradients w.r.t. the four images, written once and shared by both arms (same torch launches
+    on either side of the comparison)."""
+    loss, cots = None, []
+    for a, b in ((color, tgt[0:3]), (normal, tgt[3:6]), (depth, tgt[6:7]), (opac, tgt[7:8])):
+        d = a.detach() - b
+        part = (d * d).mean()
+        loss = part if loss is None else loss + part
+        cots.append(d * (2.0 / d.numel()))
+    return loss, cots
 
 
 class SoarArm:
@@ -236,10 +254,9 @@ class SoarArm:
 
     def view_e2e(self, cam_flat, tgt):
         color, normal, depth, opac, _ = self._render(cam_flat)
-        loss = (((color - tgt[0:3]) ** 2).mean() + ((normal - tgt[3:6]) ** 2).mean()
-                + ((depth - tgt[6:7]) ** 2).mean() + ((opac - tgt[7:8]) ** 2).mean())
-        loss.backward()
-        return loss.detach()
+        loss, cots = loss_and_cotangents(color, normal, depth, opac, tgt)
+        torch.autograd.backward([color, normal, depth, opac], cots)
+        return loss
 
 
 class ReferenceArm:
@@ -269,10 +286,8 @@ class ReferenceArm:
     def view_e2e(self, cam_flat, tgt):
         s = self.wl.scene_dict(cam_flat)
         o = self.ref.forward(s, sync=False)
-        parts = ((o["color"], tgt[0:3]), (o["normal"], tgt[3:6]), (o["depth"], tgt[6:7]), (o["opac"], tgt[7:8]))
-        loss = sum(((a - b) ** 2).mean() for a, b in parts)
-        cot = {k: (2.0 / a.numel()) * (a - b) for k, (a, b) in zip(("color", "normal", "depth", "opac"), parts)}
-        self._accumulate(self.ref.backward(cot, sync=False))
+        loss, cots = loss_and_cotangents(o["color"], o["normal"], o["depth"], o["opac"], tgt)
+        self._accumulate(self.ref.backward(dict(zip(("color", "normal", "depth", "opac"), cots)), sync=False))
         return loss
 
 
@@ -313,18 +328,33 @@ def _stage_view(wl, step, v, slot):
         wl.copied[slot].record(wl.copy_stream)
 
 
+def _prefetch_pipelined(wl, step):
+    """Enqueue, on the copy stream, the inputs step `step` needs first: its cameras (35 floats each,
+    double buffered over steps) and the target images of its first view."""
+    buf = step & 1
+    with torch.cuda.stream(wl.copy_stream):
+        wl.copy_stream.wait_event(wl.cams_consumed[buf])
+        for v in range(wl.vpr):
+            wl.cam_all[buf][v].copy_(wl.cam_host[wl.view_index(step, v)], non_blocking=True)
+        wl.cams_copied[buf].record(wl.copy_stream)
+        wl.copy_stream.wait_event(wl.consumed[0])
+        wl.tgt_dev[0].copy_(wl.tgt_host[wl.view_index(step, 0) % len(wl.tgt_host)], non_blocking=True)
+        wl.copied[0].record(wl.copy_stream)
+    wl.prefetched = step
+
+
 def step_e2e_pipelined(arm, wl, step):
-    """The e2e step on the product's multi-view path: this step's cameras are copied first (35
-    floats each) so phase 1 of every view can be enqueued up front; target images stay double
-    buffered on the copy stream; gradients accumulate in place in the flat buffer."""
+    """The e2e step on the product's multi-view path: phase 1 of every view is enqueued up front;
+    target images are double buffered on the copy stream, one view ahead — across the step boundary
+    too (the next step's cameras and first target are requested before this step's loss is read
+    back, like any input pipeline; every step still copies exactly one step's inputs inside the
+    timed region); gradients accumulate in place in the flat buffer."""
     from soar_b200.views import iter_views
     wl.flat.zero_()
     main = torch.cuda.current_stream()
-    with torch.cuda.stream(wl.copy_stream):
-        wl.copy_stream.wait_event(wl.cams_consumed)
-        for v in range(wl.vpr):
-            wl.cam_all[v].copy_(wl.cam_host[wl.view_index(step, v)], non_blocking=True)
-        wl.cams_copied.record(wl.copy_stream)
+    if wl.prefetched != step:
+        _prefetch_pipelined(wl, step)
+    buf = step & 1
 
     def stage_target(v, slot):
         with torch.cuda.stream(wl.copy_stream):
@@ -333,9 +363,8 @@ def step_e2e_pipelined(arm, wl, step):
             wl.tgt_dev[slot].copy_(wl.tgt_host[i % len(wl.tgt_host)], non_blocking=True)
             wl.copied[slot].record(wl.copy_stream)
 
-    stage_target(0, 0)
-    main.wait_event(wl.cams_copied)
-    rs, kws = zip(*(arm._rasterizer(wl.cam_all[v]) for v in range(wl.vpr)))
+    main.wait_event(wl.cams_copied[buf])
+    rs, kws = zip(*(arm._rasterizer(wl.cam_all[buf][v]) for v in range(wl.vpr)))
     total = None
     with wl.flat.direct():
         for v, (color, normal, depth, opac, _) in enumerate(iter_views(rs, kws)):
@@ -343,14 +372,13 @@ def step_e2e_pipelined(arm, wl, step):
             if v + 1 < wl.vpr:
                 stage_target(v + 1, slot ^ 1)
             main.wait_event(wl.copied[slot])
-            tgt = wl.tgt_dev[slot]
-            loss = (((color - tgt[0:3]) ** 2).mean() + ((normal - tgt[3:6]) ** 2).mean()
-                    + ((depth - tgt[6:7]) ** 2).mean() + ((opac - tgt[7:8]) ** 2).mean())
-            loss.backward()
+            loss, cots = loss_and_cotangents(color, normal, depth, opac, wl.tgt_dev[slot])
+            torch.autograd.backward([color, normal, depth, opac], cots)
             wl.consumed[slot].record(main)
-            total = loss.detach() if total is None else total + loss.detach()
-    wl.cams_consumed.record(main)
+            total = loss if total is None else total + loss
+    wl.cams_consumed[buf].record(main)
     wl.flat.allreduce()
+    _prefetch_pipelined(wl, step + 1)
     wl.loss_host.copy_(total.reshape(1), non_blocking=True)
     torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
     return float(wl.loss_host[0])
@@ -362,7 +390,8 @@ def step_e2e(arm, wl, step):
     wl.flat.zero_()
     total = None
     main = torch.cuda.current_stream()
-    _stage_view(wl, step, 0, 0)
+    if wl.prefetched != step:
+        _stage_view(wl, step, 0, 0)
     for v in range(wl.vpr):
         slot = v & 1
         if v + 1 < wl.vpr:
@@ -372,6 +401,8 @@ def step_e2e(arm, wl, step):
         wl.consumed[slot].record(main)
         total = loss if total is None else total + loss
     wl.flat.allreduce()
+    _stage_view(wl, step + 1, 0, 0)  # the next step's first view, same prefetch as the pipelined path
+    wl.prefetched = step + 1
     wl.loss_host.copy_(total.reshape(1), non_blocking=True)
     torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
     return float(wl.loss_host[0])
