@@ -212,38 +212,34 @@ knn_search_kernel(int P, const float4* __restrict__ sorted, const Aabb* __restri
       keep3(me, sorted[i], best);
     }
   }
-  const float reject = best[2];
-  best[0] = best[1] = best[2] = FLT_MAX;
-
-  for (int b2 = 0; b2 < n2; ++b2) {
+  // The traversal keeps the seed's three distances (the own leaf is not visited again) and walks
+  // every level starting with the warp's own box, so the bound tightens on the nearest leaves
+  // before the distant boxes are tested against it. Any order finds the same three smallest
+  // distances. idx >> 5 is warp-uniform (a warp is one leaf).
+  const int own0 = idx >> 5, own1 = own0 >> 5, own2 = own1 >> 5;
+  for (int t2 = 0; t2 < n2; ++t2) {
+    const int b2 = t2 == 0 ? own2 : (t2 <= own2 ? t2 - 1 : t2);
     bool want2 = false;
-    if (valid) {
-      const float dd = box_dist2(box2[b2], me);
-      want2 = !(dd > reject || dd > best[2]);
-    }
+    if (valid) want2 = !(box_dist2(box2[b2], me) > best[2]);
     if (!__any_sync(0xffffffffu, want2)) continue;
-    const int b1_end = min(n1, (b2 + 1) * KNN_FAN);
-    for (int b1 = b2 * KNN_FAN; b1 < b1_end; ++b1) {
+    const int base1 = b2 * KNN_FAN, cnt1 = min(n1, base1 + KNN_FAN) - base1;
+    const int o1 = own1 - base1;  // position of the own box among the children (b2 == own2 only)
+    for (int t1 = 0; t1 < cnt1; ++t1) {
+      const int b1 = base1 + (b2 != own2 ? t1 : (t1 == 0 ? o1 : (t1 <= o1 ? t1 - 1 : t1)));
       bool want1 = false;
-      if (want2) {
-        const float dd = box_dist2(box1[b1], me);
-        want1 = !(dd > reject || dd > best[2]);
-      }
+      if (want2) want1 = !(box_dist2(box1[b1], me) > best[2]);
       if (!__any_sync(0xffffffffu, want1)) continue;
-      const int b0_end = min(n0, (b1 + 1) * KNN_FAN);
-      for (int b0 = b1 * KNN_FAN; b0 < b0_end; ++b0) {
+      const int base0 = b1 * KNN_FAN, cnt0 = min(n0, base0 + KNN_FAN) - base0;
+      const int o0 = own0 - base0;
+      for (int t0 = 0; t0 < cnt0; ++t0) {
+        const int b0 = base0 + (b1 != own1 ? t0 : (t0 == 0 ? o0 : (t0 <= o0 ? t0 - 1 : t0)));
+        if (b0 == own0) continue;  // scanned as the seed
         bool want0 = false;
-        if (want1) {
-          const float dd = box_dist2(box0[b0], me);
-          want0 = !(dd > reject || dd > best[2]);
-        }
+        if (want1) want0 = !(box_dist2(box0[b0], me) > best[2]);
         if (!__any_sync(0xffffffffu, want0)) continue;
         if (want0) {
           const int i_end = min(P, (b0 + 1) * KNN_LEAF);
-          for (int i = b0 * KNN_LEAF; i < i_end; ++i) {
-            if (i == idx) continue;
-            keep3(me, sorted[i], best);
-          }
+          for (int i = b0 * KNN_LEAF; i < i_end; ++i) keep3(me, sorted[i], best);
         }
       }
     }
