@@ -216,31 +216,82 @@ knn_search_kernel(int P, const float4* __restrict__ sorted, const Aabb* __restri
   // every level starting with the warp's own box, so the bound tightens on the nearest leaves
   // before the distant boxes are tested against it. Any order finds the same three smallest
   // distances. idx >> 5 is warp-uniform (a warp is one leaf).
+  //
+  // The 32 children of an opened box are first tested all at once, one child per lane, against the
+  // WARP: the bounding box of its 32 query points and the largest of their current bounds. In
+  // float arithmetic that distance is never above a lane's own box distance (subtraction, product
+  // and sum are monotone and the warp box contains every query), so a child it rejects is rejected
+  // by every lane's exact test too; only the survivors pay the 32 per-lane tests.
+  const uint32_t lane = threadIdx.x & 31;
+  Aabb wb;
+  wb.lo[0] = wb.hi[0] = me.x; wb.lo[1] = wb.hi[1] = me.y; wb.lo[2] = wb.hi[2] = me.z;
+  if (!valid) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { wb.lo[k] = FLT_MAX; wb.hi[k] = -FLT_MAX; }
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      wb.lo[k] = fminf(wb.lo[k], __shfl_xor_sync(0xffffffffu, wb.lo[k], o));
+      wb.hi[k] = fmaxf(wb.hi[k], __shfl_xor_sync(0xffffffffu, wb.hi[k], o));
+    }
+  }
+  auto warp_bound = [&]() {
+    float r = valid ? best[2] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+    return r;
+  };
+  auto children_mask = [&](const Aabb* boxes, int base, int cnt, float bound) {
+    bool cand = false;
+    if ((int)lane < cnt) {
+      const Aabb b = boxes[base + lane];
+      const float dx = fmaxf(0.f, fmaxf(b.lo[0] - wb.hi[0], wb.lo[0] - b.hi[0]));
+      const float dy = fmaxf(0.f, fmaxf(b.lo[1] - wb.hi[1], wb.lo[1] - b.hi[1]));
+      const float dz = fmaxf(0.f, fmaxf(b.lo[2] - wb.hi[2], wb.lo[2] - b.hi[2]));
+      cand = !(dx * dx + dy * dy + dz * dz > bound);
+    }
+    return __ballot_sync(0xffffffffu, cand);
+  };
+  // next child of `mask`: the own box first (when it is among them), then ascending
+  auto take = [](uint32_t& mask, int own_pos) {
+    int t = (own_pos >= 0 && own_pos < 32 && ((mask >> own_pos) & 1u)) ? own_pos : __ffs(mask) - 1;
+    mask &= ~(1u << t);
+    return t;
+  };
+  float wr = warp_bound();
   const int own0 = idx >> 5, own1 = own0 >> 5, own2 = own1 >> 5;
-  for (int t2 = 0; t2 < n2; ++t2) {
-    const int b2 = t2 == 0 ? own2 : (t2 <= own2 ? t2 - 1 : t2);
-    bool want2 = false;
-    if (valid) want2 = !(box_dist2(box2[b2], me) > best[2]);
-    if (!__any_sync(0xffffffffu, want2)) continue;
-    const int base1 = b2 * KNN_FAN, cnt1 = min(n1, base1 + KNN_FAN) - base1;
-    const int o1 = own1 - base1;  // position of the own box among the children (b2 == own2 only)
-    for (int t1 = 0; t1 < cnt1; ++t1) {
-      const int b1 = base1 + (b2 != own2 ? t1 : (t1 == 0 ? o1 : (t1 <= o1 ? t1 - 1 : t1)));
-      bool want1 = false;
-      if (want2) want1 = !(box_dist2(box1[b1], me) > best[2]);
-      if (!__any_sync(0xffffffffu, want1)) continue;
-      const int base0 = b1 * KNN_FAN, cnt0 = min(n0, base0 + KNN_FAN) - base0;
-      const int o0 = own0 - base0;
-      for (int t0 = 0; t0 < cnt0; ++t0) {
-        const int b0 = base0 + (b1 != own1 ? t0 : (t0 == 0 ? o0 : (t0 <= o0 ? t0 - 1 : t0)));
-        if (b0 == own0) continue;  // scanned as the seed
-        bool want0 = false;
-        if (want1) want0 = !(box_dist2(box0[b0], me) > best[2]);
-        if (!__any_sync(0xffffffffu, want0)) continue;
-        if (want0) {
-          const int i_end = min(P, (b0 + 1) * KNN_LEAF);
-          for (int i = b0 * KNN_LEAF; i < i_end; ++i) keep3(me, sorted[i], best);
+  for (int c2 = 0; c2 < n2; c2 += 32) {
+    uint32_t m2 = children_mask(box2, c2, min(32, n2 - c2), wr);
+    while (m2) {
+      const int b2 = c2 + take(m2, own2 - c2);
+      bool want2 = false;
+      if (valid) want2 = !(box_dist2(box2[b2], me) > best[2]);
+      if (!__any_sync(0xffffffffu, want2)) continue;
+      const int base1 = b2 * KNN_FAN;
+      uint32_t m1 = children_mask(box1, base1, min(n1, base1 + KNN_FAN) - base1, wr);
+      while (m1) {
+        const int b1 = base1 + take(m1, b2 == own2 ? own1 - base1 : -1);
+        bool want1 = false;
+        if (want2) want1 = !(box_dist2(box1[b1], me) > best[2]);
+        if (!__any_sync(0xffffffffu, want1)) continue;
+        const int base0 = b1 * KNN_FAN;
+        uint32_t m0 = children_mask(box0, base0, min(n0, base0 + KNN_FAN) - base0, wr);
+        if (b1 == own1) m0 &= ~(1u << (own0 - base0));  // scanned as the seed
+        bool scanned = false;
+        while (m0) {
+          const int b0 = base0 + take(m0, -1);
+          bool want0 = false;
+          if (want1) want0 = !(box_dist2(box0[b0], me) > best[2]);
+          if (!__any_sync(0xffffffffu, want0)) continue;
+          if (want0) {
+            const int i_end = min(P, (b0 + 1) * KNN_LEAF);
+            for (int i = b0 * KNN_LEAF; i < i_end; ++i) keep3(me, sorted[i], best);
+          }
+          scanned = true;
         }
+        if (scanned) wr = warp_bound();  // the bounds only shrink: a stale value stays conservative
       }
     }
   }
