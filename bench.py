@@ -349,7 +349,7 @@ def step_e2e_pipelined(arm, wl, step):
     too (the next step's cameras and first target are requested before this step's loss is read
     back, like any input pipeline; every step still copies exactly one step's inputs inside the
     timed region); gradients accumulate in place in the flat buffer."""
-    from soar_b200.views import iter_views
+    from soar_b200.views import iter_view_pairs
     wl.flat.zero_()
     main = torch.cuda.current_stream()
     if wl.prefetched != step:
@@ -364,10 +364,10 @@ def step_e2e_pipelined(arm, wl, step):
             wl.copied[slot].record(wl.copy_stream)
 
     main.wait_event(wl.cams_copied[buf])
-    rs, kws = zip(*(arm._rasterizer(wl.cam_all[buf][v]) for v in range(wl.vpr)))
+    pairs = (arm._rasterizer(wl.cam_all[buf][v]) for v in range(wl.vpr))  # built lazily, view by view
     total = None
     with wl.flat.direct():
-        for v, (color, normal, depth, opac, _) in enumerate(iter_views(rs, kws)):
+        for v, (color, normal, depth, opac, _) in enumerate(iter_view_pairs(pairs)):
             slot = v & 1
             if v + 1 < wl.vpr:
                 stage_target(v + 1, slot ^ 1)

@@ -45,10 +45,18 @@ def iter_views(rasterizers, calls):
     (TS/renderer/gaussian_batch_renderer.py:273-323) blocks the host once per view on
     num_rendered (rasterizer_impl.cu:250) with nothing queued behind it; here only the first
     view of a step waits."""
-    rasterizers, calls = list(rasterizers), list(calls)
-    for r, kw in zip(rasterizers, calls):
+    return iter_view_pairs(zip(rasterizers, calls))
+
+
+def iter_view_pairs(pairs):
+    """iter_views over an iterable of (rasterizer, forward-kwargs) pairs. The iterable is consumed
+    lazily: with a generator, view k's settings and tensors are built while the device already runs
+    phase 1 of view k-1, so the first kernels of a step are enqueued as early as possible."""
+    started = []
+    for r, kw in pairs:
         r.begin(**kw)
-    for r, kw in zip(rasterizers, calls):
+        started.append((r, kw))
+    for r, kw in started:
         yield r(**kw)
 
 
