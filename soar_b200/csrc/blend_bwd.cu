@@ -19,6 +19,7 @@
 //     forward blend left in the binning buffer, so a culled entry costs a one-byte load;
 //   * pixel-constant factors are hoisted, 1/(1-alpha) is formed once per contribution, and
 //     the body is specialised on (surface, per-pixel depth, normalize_depth).
+#include <stdlib.h>
 #include "common.cuh"
 #include "layout.h"
 #include "kernels.h"
@@ -347,6 +348,271 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Two pixels per thread (the forward's blend_fwd2 layout: 128-thread CTAs, warp = 8x8 pixel block =
+// two 8x4 mask blocks, lane (lx, ly) replays pixels (lx, ly) and (lx, ly + 4)) with packed f32x2
+// arithmetic. Per (Gaussian, 8x8 block) the loop control, the shared loads and — the point of it —
+// the warp reduction of the 10 / 14 partials are paid ONCE for 64 pixels instead of once per 32: the
+// two pixels' partials are added in the lane before the butterfly. Same formulas as blend_bwd_body;
+// the sums are associated differently (pixel pair first), which is inside the 1e-3 contract.
+// ---------------------------------------------------------------------------------------------
+constexpr int BWD2_THREADS = TILE_PIX / 2;
+
+__device__ __forceinline__ float2 bc(float s) { return make_float2(s, s); }
+
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+__device__ __forceinline__ void blend_bwd2_body(const BlendBwdArgs& a, BlendBwdSmem& sm) {
+  const int tid = threadIdx.x;
+  const uint32_t lane = tid & 31, warp = tid >> 5;
+  const uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y;
+  const uint32_t px = tile_x * TILE_X + (warp & 1u) * 8u + (lane & 7u);
+  const uint32_t py0 = tile_y * TILE_Y + (warp >> 1) * 8u + (lane >> 3);
+  const uint32_t py1 = py0 + 4u;
+  const bool inside0 = px < (uint32_t)a.W && py0 < (uint32_t)a.H;
+  const bool inside1 = px < (uint32_t)a.W && py1 < (uint32_t)a.H;
+  const uint32_t pix0 = (uint32_t)a.W * py0 + px, pix1 = (uint32_t)a.W * py1 + px;
+  const float pxf = (float)px;
+  const float2 npyf = make_float2(-(float)py0, -(float)py1);
+  const size_t HW = (size_t)a.H * a.W;
+  const uint32_t wA = 4u * (warp >> 1) + (warp & 1u);
+  const uint32_t my_blocks = 5u << wA;
+
+  const uint2 range = a.ranges[tile_y * a.grid_x + tile_x];
+  if (range.y == range.x) return;
+
+  // lanes outside the image never contribute; 0.5 keeps their (discarded) arithmetic finite
+  const float2 T_final = make_float2(inside0 ? a.final_T[pix0] : 0.5f, inside1 ? a.final_T[pix1] : 0.5f);
+  const float2 D_final = make_float2(inside0 && NORM_DEPTH ? a.final_D[pix0] : 0.f,
+                                     inside1 && NORM_DEPTH ? a.final_D[pix1] : 0.f);
+  const uint32_t last0 = inside0 ? a.n_contrib[pix0] : 0, last1 = inside1 ? a.n_contrib[pix1] : 0;
+
+  uint32_t block_depth = max(last0, last1);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    block_depth = max(block_depth, __shfl_xor_sync(0xffffffffu, block_depth, o));
+  if (lane == 0) sm.max_contrib[warp] = block_depth;
+  __syncthreads();
+  uint32_t tile_depth = 0;
+#pragma unroll
+  for (int w = 0; w < BWD2_THREADS / 32; ++w) tile_depth = max(tile_depth, sm.max_contrib[w]);
+  if (tile_depth == 0) return;
+  const uint32_t list_end = range.x + tile_depth;
+  const int rounds = (tile_depth + BWD_BATCH - 1) / BWD_BATCH;
+
+  float2 gC0 = bc(0.f), gC1 = gC0, gC2 = gC0, gN0 = gC0, gN1 = gC0, gN2 = gC0, gD = gC0, gO = gC0;
+  if (inside0) {
+    gC0.x = a.dL_dpixcolor[0 * HW + pix0]; gC1.x = a.dL_dpixcolor[1 * HW + pix0]; gC2.x = a.dL_dpixcolor[2 * HW + pix0];
+    if (SURFACE) { gN0.x = a.dL_dpixnormal[0 * HW + pix0]; gN1.x = a.dL_dpixnormal[1 * HW + pix0]; gN2.x = a.dL_dpixnormal[2 * HW + pix0]; }
+    gD.x = a.dL_dpixdepth[pix0] * 1;
+    gO.x = a.dL_dpixopac[pix0];
+  }
+  if (inside1) {
+    gC0.y = a.dL_dpixcolor[0 * HW + pix1]; gC1.y = a.dL_dpixcolor[1 * HW + pix1]; gC2.y = a.dL_dpixcolor[2 * HW + pix1];
+    if (SURFACE) { gN0.y = a.dL_dpixnormal[0 * HW + pix1]; gN1.y = a.dL_dpixnormal[1 * HW + pix1]; gN2.y = a.dL_dpixnormal[2 * HW + pix1]; }
+    gD.y = a.dL_dpixdepth[pix1] * 1;
+    gO.y = a.dL_dpixopac[pix1];
+  }
+  float2 bg_dot = bc(0.f);
+  bg_dot = __ffma2_rn(bc(a.bg[0]), gC0, bg_dot);
+  bg_dot = __ffma2_rn(bc(a.bg[1]), gC1, bg_dot);
+  bg_dot = __ffma2_rn(bc(a.bg[2]), gC2, bg_dot);
+
+  // pixel constants of the depth terms, as in blend_bwd_body
+  float2 g_depth_ch = gD, norm_k = bc(0.f);
+  if (NORM_DEPTH) {
+    g_depth_ch = make_float2(gD.x / (1.f - T_final.x), gD.y / (1.f - T_final.y));
+    norm_k = make_float2(gD.x * D_final.x / (1.f - T_final.x) / (1.f - T_final.x) * -T_final.x,
+                         gD.y * D_final.y / (1.f - T_final.y) / (1.f - T_final.y) * -T_final.y);
+  }
+  float2 tf_k = make_float2(gO.x * T_final.x - T_final.x * bg_dot.x, gO.y * T_final.y - T_final.y * bg_dot.y);
+  if (!NORM_DEPTH) {
+    tf_k.x -= T_final.x * (10 * gD.x);
+    tf_k.y -= T_final.y * (10 * gD.y);
+  }
+
+  float2 T = T_final, S = bc(0.f), cg_last = bc(0.f), last_alpha = bc(0.f);
+
+  for (int i = 0; i < rounds; i++) {
+    // ---- stage two entries per thread (from the back), compact in walk order ---------------
+    uint32_t mask[2] = {0, 0}, id[2] = {0, 0};
+    const float4* rec[2] = {nullptr, nullptr};
+    float4 q0[2], q1[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const uint32_t progress = i * BWD_BATCH + h * BWD2_THREADS + tid;
+      if (progress < tile_depth) {
+        mask[h] = a.pair_mask[list_end - progress - 1];
+        if (mask[h] != 0) {
+          id[h] = a.point_list[list_end - progress - 1];
+          rec[h] = reinterpret_cast<const float4*>(a.records + (size_t)id[h] * REC_FLOATS);
+          q0[h] = __ldg(rec[h] + 0);
+          q1[h] = __ldg(rec[h] + 1);
+        }
+      }
+    }
+    uint32_t keep_ballot[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      keep_ballot[h] = __ballot_sync(0xffffffffu, mask[h] != 0);
+      if (lane == 0) sm.wcount[h * 4 + warp] = __popc(keep_ballot[h]);
+    }
+    __syncthreads();
+    uint32_t slot[2] = {__popc(keep_ballot[0] & lanemask_lt()), __popc(keep_ballot[1] & lanemask_lt())};
+    uint32_t n = 0;
+#pragma unroll
+    for (uint32_t w = 0; w < N_BLK; ++w) {
+      const uint32_t c = sm.wcount[w];
+      if (w < warp) slot[0] += c;
+      if (w < 4u + warp) slot[1] += c;
+      n += c;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (mask[h] != 0) {
+        const uint32_t sl = slot[h];
+        sm.q0[sl] = q0[h];
+        sm.q1[sl] = q1[h];
+        sm.q2[sl] = __ldg(rec[h] + 2);
+        if (SURFACE) sm.q3[sl] = __ldg(rec[h] + 3);
+        if (DEPTH_DIFF) sm.q4[sl] = __ldg(rec[h] + 4);
+        sm.id[sl] = id[h];
+        sm.pos[sl] = tile_depth - 1 - (i * BWD_BATCH + h * BWD2_THREADS + tid);
+        sm.mask[sl] = (uint8_t)mask[h];
+      }
+    }
+    __syncthreads();
+
+    for (uint32_t c0 = 0; c0 < n; c0 += 32) {
+      const uint32_t jj = c0 + lane;
+      const bool mine = jj < n && (sm.mask[jj] & my_blocks) && sm.pos[jj] < block_depth;
+      uint32_t bits = __ballot_sync(0xffffffffu, mine);
+      while (bits) {
+        const uint32_t j = c0 + __ffs(bits) - 1;
+        bits &= bits - 1;
+        const uint32_t pos = sm.pos[j];
+        bool live0 = pos < last0, live1 = pos < last1;
+        const float4 q0j = sm.q0[j];
+        const float4 q1j = sm.q1[j];
+        const float dx = q0j.x - pxf;
+        const float2 dy = __fadd2_rn(bc(q0j.y), npyf);
+        const float adx = q0j.z * dx;
+        const float bdx = dx * (q0j.w + q0j.w);
+        const float2 cdy = __fmul2_rn(bc(q1j.x), dy);
+        float2 dist = __fmul2_rn(dy, cdy);
+        dist = __ffma2_rn(bc(dx), bc(adx), dist);
+        dist = __ffma2_rn(dy, bc(bdx), dist);
+        const float2 power = __fmul2_rn(dist, bc(-0.5f));
+        live0 = live0 && !(power.x > 0.0f) && !(power.x < q1j.z);
+        live1 = live1 && !(power.y > 0.0f) && !(power.y < q1j.z);
+        if (!__any_sync(0xffffffffu, live0 || live1)) continue;
+        const float2 pl = __fmul2_rn(power, bc(1.4426950408889634f));
+        const float2 G = make_float2(ex2_approx(pl.x), ex2_approx(pl.y));
+        const float2 og = __fmul2_rn(bc(q1j.y), G);
+        float2 alpha = make_float2(min(0.99f, og.x), min(0.99f, og.y));
+        live0 = live0 && !(alpha.x < 1.0f / 255.0f);
+        live1 = live1 && !(alpha.y < 1.0f / 255.0f);
+        if (!__any_sync(0xffffffffu, live0 || live1)) continue;
+
+        // lanes that do not contribute run the same arithmetic with alpha = 0 and G = 0
+        alpha.x = live0 ? alpha.x : 0.f;
+        alpha.y = live1 ? alpha.y : 0.f;
+        const float2 Gl = make_float2(live0 ? G.x : 0.f, live1 ? G.y : 0.f);
+        float v[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = 0.f;
+        {
+          const float2 T_behind = T;
+          const float2 oma = __fadd2_rn(bc(1.f), make_float2(-alpha.x, -alpha.y));
+          const float2 rcp = make_float2(rcp_approx(oma.x), rcp_approx(oma.y));
+          T = __fmul2_rn(T, rcp);
+          const float2 dch = __fmul2_rn(alpha, T);
+          const float4 q2 = sm.q2[j];
+
+          float2 cg = __fmul2_rn(bc(q2.x), gC0);
+          cg = __ffma2_rn(bc(q2.y), gC1, cg);
+          cg = __ffma2_rn(bc(q2.z), gC2, cg);
+          const float2 vC0 = __fmul2_rn(dch, gC0), vC1 = __fmul2_rn(dch, gC1), vC2 = __fmul2_rn(dch, gC2);
+          v[LS_DC0] = vC0.x + vC0.y;
+          v[LS_DC1] = vC1.x + vC1.y;
+          v[LS_DC2] = vC2.x + vC2.y;
+          float2 d_cur = bc(q1j.w);
+          if (SURFACE) {
+            const float4 q3 = sm.q3[j];
+            cg = __ffma2_rn(bc(q3.x), gN0, cg);
+            cg = __ffma2_rn(bc(q3.y), gN1, cg);
+            cg = __ffma2_rn(bc(q3.z), gN2, cg);
+            const float2 dch10 = __fmul2_rn(dch, bc(10.f));
+            const float2 vN0 = __fmul2_rn(dch10, gN0), vN1 = __fmul2_rn(dch10, gN1), vN2 = __fmul2_rn(dch10, gN2);
+            v[LS_DN0] = vN0.x + vN0.y;
+            v[LS_DN1] = vN1.x + vN1.y;
+            v[LS_DN2] = vN2.x + vN2.y;
+            if (DEPTH_DIFF) {
+              const float4 q4 = sm.q4[j];
+              // dif_u0 = dx J0 + dy J1, dif_u1 = dx J2 + dy J3, d_cur -= dif_u0 J6 + dif_u1 J9
+              const float2 u0 = __ffma2_rn(dy, bc(q4.y), bc(dx * q4.x));
+              const float2 u1 = __ffma2_rn(dy, bc(q4.w), bc(dx * q4.z));
+              const float2 dz = __ffma2_rn(u1, bc(q3.w), __fmul2_rn(u0, bc(q2.w)));
+              d_cur = __fadd2_rn(d_cur, make_float2(-dz.x, -dz.y));
+              v[LS_GD] = (live0 ? gD.x : 0.f) + (live1 ? gD.y : 0.f);
+            }
+          }
+          cg = __ffma2_rn(d_cur, g_depth_ch, cg);
+          const float2 vDD = __fmul2_rn(dch, g_depth_ch);
+          v[LS_DD] = vDD.x + vDD.y;
+          // S <- last_alpha * cg_last + (1 - last_alpha) * S
+          const float2 oml = __fadd2_rn(bc(1.f), make_float2(-last_alpha.x, -last_alpha.y));
+          S = __ffma2_rn(last_alpha, cg_last, __fmul2_rn(oml, S));
+          cg_last = cg;
+          float2 dL_dalpha = __fadd2_rn(cg, make_float2(-S.x, -S.y));
+          if (NORM_DEPTH) {
+            dL_dalpha.x += norm_k.x / T_behind.x;
+            dL_dalpha.y += norm_k.y / T_behind.y;
+          }
+          dL_dalpha = __fmul2_rn(dL_dalpha, T);
+          dL_dalpha = __ffma2_rn(tf_k, rcp, dL_dalpha);
+          last_alpha = alpha;
+
+          const float2 gda = __fmul2_rn(Gl, dL_dalpha);
+          const float2 dL_ddist = __fmul2_rn(__fmul2_rn(gda, bc(q1j.y)), bc(-0.5f));
+          const float2 ddx = __fmul2_rn(dL_ddist, bc(dx)), ddy = __fmul2_rn(dL_ddist, dy);
+          const float2 mxx = __fmul2_rn(ddx, bc(dx)), mxy = __fmul2_rn(ddx, dy), myy = __fmul2_rn(ddy, dy);
+          v[LS_DO] = gda.x + gda.y;
+          v[LS_MX] = ddx.x + ddx.y;
+          v[LS_MY] = ddy.x + ddy.y;
+          v[LS_MXX] = mxx.x + mxx.y;
+          v[LS_MXY] = mxy.x + mxy.y;
+          v[LS_MYY] = myy.x + myy.y;
+        }
+
+        float* const g = a.gacc + (size_t)sm.id[j] * GACC_FLOATS;
+        if (SURFACE) {
+          const float total = warp_reduce16(v, lane);
+          if ((lane & 1) == 0 && (lane >> 1) < LS_COUNT) atomicAdd(g + (lane >> 1), total);
+        } else {
+          int slot_idx;
+          const float total = warp_reduce10(v, lane, slot_idx);
+          if (slot_idx >= 0) atomicAdd(g + slot_idx, total);
+        }
+      }
+    }
+  }
+}
+
+template <bool SURFACE, bool DEPTH_DIFF>
+__device__ __forceinline__ void blend_bwd2_pick(const BlendBwdArgs& a, BlendBwdSmem& sm, bool normalize_depth) {
+  if (normalize_depth) blend_bwd2_body<SURFACE, DEPTH_DIFF, true>(a, sm);
+  else blend_bwd2_body<SURFACE, DEPTH_DIFF, false>(a, sm);
+}
+
+__global__ void __launch_bounds__(BWD2_THREADS, 6) blend_bwd2_kernel(const BlendBwdArgs a) {
+  __shared__ BlendBwdSmem sm;
+  const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
+             normalize_depth = a.config[1] > 0;
+  if (surface && per_pixel_depth) blend_bwd2_pick<true, true>(a, sm, normalize_depth);
+  else if (surface) blend_bwd2_pick<true, false>(a, sm, normalize_depth);
+  else blend_bwd2_pick<false, false>(a, sm, normalize_depth);
+}
+
 // The config flags live in device memory (backward.cu:581): one kernel, specialised bodies
 // selected by a uniform branch.
 __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdArgs a) {
@@ -369,7 +635,8 @@ int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream) {
   dim3 grid(a.grid_x, grid_y, 1);
   {
     KernelScope ks(K_BLEND_BWD, stream);
-    blend_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(a);
+    if (getenv("SOAR_BLEND_BWD_SCALAR")) blend_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(a);
+    else blend_bwd2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(a);
   }
   SOAR_LAUNCH_CHECK("blend_bwd_kernel");
   return SOAR_OK;
