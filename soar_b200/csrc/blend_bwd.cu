@@ -604,7 +604,7 @@ __device__ __forceinline__ void blend_bwd2_pick(const BlendBwdArgs& a, BlendBwdS
   else blend_bwd2_body<SURFACE, DEPTH_DIFF, false>(a, sm);
 }
 
-__global__ void __launch_bounds__(BWD2_THREADS, 6) blend_bwd2_kernel(const BlendBwdArgs a) {
+__global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel(const BlendBwdArgs a) {
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;

@@ -51,7 +51,8 @@ def main():
         # per-launch DRAM traffic of the largest launch of every kernel -> bench.py roofline.traffic
         names = {"preprocess_fwd_kernel": "preprocess_fwd", "duplicate_tiles_kernel": "duplicate_keys",
                  "radix_onesweep_kernel": "radix_onesweep", "blend_fwd_kernel": "blend_fwd",
-                 "blend_bwd_kernel": "blend_bwd", "geom_bwd_kernel": "geom_bwd"}
+                 "blend_bwd_kernel": "blend_bwd", "geom_bwd_kernel": "geom_bwd",
+                 "blend_fwd2_kernel": "blend_fwd", "blend_bwd2_kernel": "blend_bwd"}
         scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         ir, iw = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
         traffic = {}
