@@ -20,6 +20,8 @@ namespace soar {
 // SHV: SH coefficients per Gaussian fetched with 16-byte loads (16 or 4); 0 = scalar path.
 // 128 threads x 6 CTAs/SM under an 85-register cap (28 B of spill): 768 threads of loads in flight per SM
 // instead of 512 (the uncapped build takes 89 registers).
+// (Fetching the thread's SH row with cp.async into shared memory at kernel start, awaited only where
+// the colour is evaluated, was measured: 51 vs 46 us — not done.)
 constexpr int PP_THREADS = 128;
 template <int SHV>
 __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const PreprocessArgs a) {
