@@ -142,3 +142,21 @@ def test_view_sharded_gradients_equal_single_rank_gloo(tmp_path):
         got = torch.load(os.path.join(tmp_path, f"rank{r}.pt"))
         for k in want:
             assert torch.allclose(got[k], want[k], rtol=1e-5, atol=1e-5), (r, k)
+
+
+def test_bench_loss_helper_matches_autograd():
+    """bench.py's e2e step feeds the rasterizer backward with explicit cotangents: they must be the
+    gradients autograd would produce for the same sum of mean squared errors."""
+    import importlib
+    import torch
+    bench = importlib.import_module("bench")
+    torch.manual_seed(0)
+    outs = [torch.randn(3, 8, 8, requires_grad=True), torch.randn(3, 8, 8, requires_grad=True),
+            torch.randn(1, 8, 8, requires_grad=True), torch.randn(1, 8, 8, requires_grad=True)]
+    tgt = torch.randn(8, 8, 8)
+    loss, cots = bench.loss_and_cotangents(*outs, tgt)
+    ref = sum(((o - t) ** 2).mean() for o, t in zip(outs, (tgt[0:3], tgt[3:6], tgt[6:7], tgt[7:8])))
+    grads = torch.autograd.grad(ref, outs)
+    assert torch.allclose(loss, ref.detach(), rtol=1e-6, atol=0)
+    for c, g in zip(cots, grads):
+        assert torch.allclose(c, g, rtol=1e-6, atol=1e-9)
