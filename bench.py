@@ -40,10 +40,24 @@ import torch
 import torch.distributed as dist
 
 WORKLOADS = {
-    # name: (P, W, H, sh_degree)
-    "c3": (500_000, 1024, 1024, 3),
-    "c2": (100_000, 512, 512, 0),
-    "tiny": (20_000, 256, 256, 1),
+    # rasterizer workloads: P Gaussians, WxH, SH degree (None = precomputed colour), cloud, and either
+    # views=None -> weak scaling (`--views-per-rank` views per rank and step, 8 cameras per rank cycling)
+    # or views=V -> strong scaling (V views per step, sharded over the ranks with shard_views)
+    "c3": dict(P=500_000, W=1024, H=1024, deg=3, cloud="random", views=None,
+               text="single-view rasterizer fwd+bwd, 1024x1024, 500000 Gaussians, SH degree 3"),
+    "c2": dict(P=100_000, W=512, H=512, deg=0, cloud="random", views=None,
+               text="single-view rasterizer fwd+bwd, 512x512, 100000 Gaussians, SH degree 0"),
+    "tiny": dict(P=20_000, W=256, H=256, deg=1, cloud="random", views=None,
+                 text="single-view rasterizer fwd+bwd, 256x256, 20000 Gaussians, SH degree 1"),
+    # BASELINE configs[3]: the SDS multi-view step (TS/renderer/gaussian_batch_renderer.py:273-323)
+    "c4": dict(P=100_000, W=512, H=512, deg=None, cloud="avatar", views=32,
+               text="SDS multi-view step: 32 views at 512x512 of 100000 avatar surfels (config 1,1,1,0), "
+                    "view-sharded, one gradient allreduce"),
+    # BASELINE configs[4]: the dance_0-shaped step through AvatarRenderer (see AvatarWorkload)
+    "c5": dict(P=2_000_000, W=1920, H=1080, deg=None, cloud="avatar", views=None,
+               text="dance_0-shaped step: 2000000 skinned avatar surfels at 1920x1080, per rank one video "
+                    "frame = KNN + pose + weight query + 3 gt views (rgb, front normal, back normal: skin, "
+                    "rasterizer + occupancy pass, post-ops, backward)"),
 }
 
 
@@ -61,6 +75,11 @@ def parse_args():
     ap.add_argument("--sequential", action="store_true",
                     help="one blocking forward+backward per view through autograd's own gradient "
                          "accumulation (no begin-all pipelining, no in-place accumulation)")
+    ap.add_argument("--no-sequential", action="store_true", help="skip the unchanged-caller figure")
+    ap.add_argument("--no-gpu-baselines", action="store_true",
+                    help="skip the reference distCUDA2 / torch LBS chain timed on this GPU")
+    ap.add_argument("--float-targets", action="store_true",
+                    help="e2e: ship the target images as float32 (r01 protocol) instead of uint8")
     return ap.parse_args()
 
 
@@ -122,19 +141,53 @@ CAMS_PER_RANK = 8
 PARAM_KEYS = ("means3D", "shs", "colors_precomp", "opacities", "scales", "rotations")
 
 
+def avatar_surfels(P, seed=0):
+    """The "avatar" cloud of SURVEY 8d without the product KNN (so the reference arm never loads the
+    product library): centres on the synthetic SMPL-X template (+ N(0, 4 mm)), random tangent frames,
+    in-plane scale U(0.5, 1.5) x 4 mm (the template's mean vertex spacing), s_z = -1e10, opacity 1."""
+    from soar_b200 import synthetic
+    m = synthetic.smplx_template(NB=1, seed=seed)
+    g = synthetic.avatar_gaussians(P, m["v_template"], seed=seed)
+    s2 = (g["scale_jitter"] * 0.004).clamp(1e-4, 0.02)
+    scales = torch.cat([s2, s2, torch.full_like(s2, -1e10)], 1).contiguous()
+    return dict(means3D=g["points"], rotations=torch.nn.functional.normalize(g["rot"], dim=1),
+                scales=scales, opacities=torch.ones(P, 1), colors_precomp=g["colors"], shs=None)
+
+
 class Workload:
-    def __init__(self, name, device, rank, world, views_per_rank):
+    def __init__(self, name, device, rank, world, views_per_rank, float_targets=False):
         from soar_b200 import synthetic
-        from soar_b200.views import FlatGrads
-        self.name = name
-        self.P, self.W, self.H, self.deg = WORKLOADS[name]
-        self.device, self.rank, self.world, self.vpr = device, rank, world, views_per_rank
+        from soar_b200.views import FlatGrads, shard_views
+        spec = WORKLOADS[name]
+        self.name, self.spec = name, spec
+        self.P, self.W, self.H, self.deg = spec["P"], spec["W"], spec["H"], spec["deg"]
+        self.device, self.rank, self.world = device, rank, world
         self.pipelined = True
-        g = synthetic.gaussians(self.P, sh_degree=self.deg, seed=0)
+        self.float_targets = float_targets
+        surfel = spec["cloud"] == "avatar"
+        if surfel:
+            g = avatar_surfels(self.P, seed=0)
+            cam_kw = dict(dist=(1.6, 2.0))
+        else:
+            g = synthetic.gaussians(self.P, sh_degree=self.deg, seed=0)
+            cam_kw = {}
         self.params = {k: g[k].to(device).requires_grad_(True) for k in PARAM_KEYS if g.get(k) is not None}
-        self.flat = FlatGrads(self.params)
-        cams = synthetic.ring_cameras(CAMS_PER_RANK * world, self.W, self.H, seed=0)
-        mine = cams[rank * CAMS_PER_RANK:(rank + 1) * CAMS_PER_RANK]
+        if surfel:
+            self.params["opacities"].requires_grad_(False)   # SOAR passes ones (renderer :254-263)
+        self.flat = FlatGrads({k: v for k, v in self.params.items() if v.requires_grad})
+        if spec["views"] is None:      # weak scaling: every rank has its own ring of cameras
+            self.vpr = views_per_rank
+            self.views_per_step = views_per_rank * world
+            cams = synthetic.ring_cameras(CAMS_PER_RANK * world, self.W, self.H, seed=0, **cam_kw)
+            mine = cams[rank * CAMS_PER_RANK:(rank + 1) * CAMS_PER_RANK]
+            self.scaling = "weak"
+        else:                          # strong scaling: V views per step over all ranks
+            V = spec["views"]
+            cams = synthetic.ring_cameras(V, self.W, self.H, seed=0, **cam_kw)
+            mine = [cams[v] for v in shard_views(V, rank, world)]
+            self.vpr, self.views_per_step = len(mine), V
+            self.scaling = "strong"
+        self.n_cams = len(mine)
         self.cam_host = []   # pinned [35]: viewmatrix 16 | projmatrix 16 | campos 3
         self.cam_dev = []
         for c in mine:
@@ -146,22 +199,28 @@ class Workload:
         self.bg = torch.zeros(3, **f32)
         self.patch_bbox = torch.tensor([0.0, 0.0, float(self.H), float(self.W)], **f32)
         self.prcppoint = torch.tensor([0.5, 0.5], **f32)
-        self.config = torch.zeros(4, **f32)
+        self.config = torch.tensor([1.0, 1.0, 1.0, 0.0] if surfel else [0.0, 0.0, 0.0, 0.0], **f32)
         cot = synthetic.cotangents(self.W, self.H, seed=0)
         self.cot = {k: v.to(device) for k, v in cot.items()}
-        # e2e: per-camera target images for the four outputs (8 channels), pinned on the host
+        # e2e: per-camera target images for the four outputs (8 channels), pinned on the host. Shipped
+        # as uint8 — what image files hold — and converted on the device (--float-targets: float32).
         gen = torch.Generator().manual_seed(1234 + rank)
-        self.tgt_host = [torch.rand((8, self.H, self.W), generator=gen).pin_memory()
-                         for _ in range(min(CAMS_PER_RANK, views_per_rank * 2))]
+        n_tgt = min(self.n_cams, self.vpr * 2)
+        self.tgt_dtype = torch.float32 if float_targets else torch.uint8
+        if float_targets:
+            self.tgt_host = [torch.rand((8, self.H, self.W), generator=gen).pin_memory() for _ in range(n_tgt)]
+        else:
+            self.tgt_host = [torch.randint(0, 256, (8, self.H, self.W), generator=gen, dtype=torch.uint8).pin_memory()
+                             for _ in range(n_tgt)]
         # e2e staging: double-buffered device copies filled by a side stream, so the host->device
         # copy of view k+1 overlaps the render of view k (both inside the timed region)
-        self.tgt_dev = [torch.empty((8, self.H, self.W), **f32) for _ in range(2)]
+        self.tgt_dev = [torch.empty((8, self.H, self.W), dtype=self.tgt_dtype, device=device) for _ in range(2)]
         self.cam_stage = [torch.empty(35, **f32) for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=device)
         self.copied = [torch.cuda.Event() for _ in range(2)]
         self.consumed = [torch.cuda.Event() for _ in range(2)]
         # cameras of a step, double buffered over steps (the next step's are prefetched)
-        self.cam_all = [[torch.empty(35, **f32) for _ in range(views_per_rank)] for _ in range(2)]
+        self.cam_all = [[torch.empty(35, **f32) for _ in range(self.vpr)] for _ in range(2)]
         self.cams_copied = [torch.cuda.Event() for _ in range(2)]
         self.cams_consumed = [torch.cuda.Event() for _ in range(2)]
         self.prefetched = None  # step whose first inputs are already on their way
@@ -175,16 +234,16 @@ class Workload:
         s.update(viewmatrix=cam_flat[0:16].view(4, 4), projmatrix=cam_flat[16:32].view(4, 4),
                  campos=cam_flat[32:35], tanfovx=self.tanfovx, tanfovy=self.tanfovy,
                  image_height=self.H, image_width=self.W, bg=self.bg, scale_modifier=1.0,
-                 patch_bbox=self.patch_bbox, prcppoint=self.prcppoint, sh_degree=self.deg,
+                 patch_bbox=self.patch_bbox, prcppoint=self.prcppoint, sh_degree=self.deg or 0,
                  prefiltered=False, render_front=False, sort_descending=False, debug=False,
                  config=self.config)
         return s
 
     def view_index(self, step, v):
-        return (step * self.vpr + v) % CAMS_PER_RANK
+        return (step * self.vpr + v) % self.n_cams
 
     def h2d_bytes_per_step(self):
-        return self.vpr * (35 * 4 + 8 * self.H * self.W * 4)
+        return self.vpr * (35 * 4 + 8 * self.H * self.W * (4 if self.float_targets else 1))
 
 
 def loss_and_cotangents(color, normal, depth, opac, tgt):
@@ -192,6 +251,8 @@ def loss_and_cotangents(color, normal, depth, opac, tgt):
     its gradients w.r.t. the four images, written once and shared by both arms (same torch launches
     on either side of the comparison)."""
     loss, cots = None, []
+    if tgt.dtype == torch.uint8:    # image bytes -> [0, 1] on the device (one launch, both arms)
+        tgt = tgt.float() * (1.0 / 255.0)
     for a, b in ((color, tgt[0:3]), (normal, tgt[3:6]), (depth, tgt[6:7]), (opac, tgt[7:8])):
         d = a.detach() - b
         part = (d * d).mean()
@@ -214,7 +275,7 @@ class SoarArm:
         st = self.S(image_height=wl.H, image_width=wl.W, tanfovx=wl.tanfovx, tanfovy=wl.tanfovy,
                     bg=wl.bg, scale_modifier=1.0, viewmatrix=cam_flat[0:16].view(4, 4),
                     projmatrix=cam_flat[16:32].view(4, 4), patch_bbox=wl.patch_bbox,
-                    prcppoint=wl.prcppoint, sh_degree=wl.deg, campos=cam_flat[32:35],
+                    prcppoint=wl.prcppoint, sh_degree=wl.deg or 0, campos=cam_flat[32:35],
                     prefiltered=False, render_front=False, sort_descending=False, debug=False,
                     config=wl.config)
         means2D = torch.zeros_like(p["means3D"], requires_grad=True)
@@ -227,7 +288,7 @@ class SoarArm:
         st = self.S(image_height=wl.H, image_width=wl.W, tanfovx=wl.tanfovx, tanfovy=wl.tanfovy,
                     bg=wl.bg, scale_modifier=1.0, viewmatrix=cam_flat[0:16].view(4, 4),
                     projmatrix=cam_flat[16:32].view(4, 4), patch_bbox=wl.patch_bbox,
-                    prcppoint=wl.prcppoint, sh_degree=wl.deg, campos=cam_flat[32:35],
+                    prcppoint=wl.prcppoint, sh_degree=wl.deg or 0, campos=cam_flat[32:35],
                     prefiltered=False, render_front=False, sort_descending=False, debug=False,
                     config=wl.config)
         p = wl.params
@@ -242,7 +303,7 @@ class SoarArm:
         from soar_b200.views import iter_views
         c = self.wl.cot
         rs, kws = zip(*(self._rasterizer(cam) for cam in cams))
-        with self.wl.flat.direct():
+        with self.wl.flat.direct(overwrite=True):   # the first view of a step stores: no zero-fill
             for color, normal, depth, opac, _ in iter_views(rs, kws):
                 torch.autograd.backward([color, normal, depth, opac],
                                         [c["color"], c["normal"], c["depth"], c["opac"]])
@@ -257,6 +318,18 @@ class SoarArm:
         loss, cots = loss_and_cotangents(color, normal, depth, opac, tgt)
         torch.autograd.backward([color, normal, depth, opac], cots)
         return loss
+
+    def stats(self, cam_flat):
+        """(P_visible, num_rendered) of one camera, outside any timed region."""
+        from diff_gaussian_rasterization import _C
+        wl, p, e = self.wl, self.wl.params, torch.Tensor([])
+        out = _C.rasterize_gaussians(
+            wl.bg, p["means3D"].detach(), p["colors_precomp"].detach() if "colors_precomp" in p else e,
+            p["opacities"].detach(), p["scales"].detach(), p["rotations"].detach(), 1.0, e,
+            cam_flat[0:16].view(4, 4), cam_flat[16:32].view(4, 4), wl.prcppoint, wl.patch_bbox, wl.tanfovx,
+            wl.tanfovy, wl.H, wl.W, p["shs"].detach() if "shs" in p else e, wl.deg or 0, cam_flat[32:35],
+            False, False, False, False, wl.config)
+        return int((out[5] > 0).sum().item()), int(out[0])
 
 
 class ReferenceArm:
@@ -275,8 +348,13 @@ class ReferenceArm:
                     "opacities": "opacity", "scales": "scales", "rotations": "rotations"}
 
     def _accumulate(self, g):
-        for k in self.wl.params:
+        for k in self.wl.flat.names:
             self.wl.flat.grad(k).add_(g[self.map[k]].view_as(self.wl.params[k]))
+
+    def stats(self, cam_flat):
+        """(P_visible, num_rendered) from the reference's own radii / num_rendered."""
+        o = self.ref.forward(self.wl.scene_dict(cam_flat))
+        return int((o["radii"] > 0).sum().item()), int(o["num_rendered"])
 
     def view_resident(self, cam_flat):
         s = self.wl.scene_dict(cam_flat)
@@ -308,14 +386,16 @@ def max_over_ranks(ms, world, device):
     return float(t.item())
 
 
-def step_resident(arm, wl, step):
-    wl.flat.zero_()
+def step_resident(arm, wl, step, allreduce=True):
     if wl.pipelined and hasattr(arm, "views_resident"):
+        # FlatGrads.direct(overwrite=True): the first backward stores, so nothing is zero-filled
         arm.views_resident([wl.cam_dev[wl.view_index(step, v)] for v in range(wl.vpr)])
     else:
+        wl.flat.zero_()
         for v in range(wl.vpr):
             arm.view_resident(wl.cam_dev[wl.view_index(step, v)])
-    wl.flat.allreduce()
+    if allreduce:
+        wl.flat.allreduce()
 
 
 def _stage_view(wl, step, v, slot):
@@ -350,7 +430,6 @@ def step_e2e_pipelined(arm, wl, step):
     back, like any input pipeline; every step still copies exactly one step's inputs inside the
     timed region); gradients accumulate in place in the flat buffer."""
     from soar_b200.views import iter_view_pairs
-    wl.flat.zero_()
     main = torch.cuda.current_stream()
     if wl.prefetched != step:
         _prefetch_pipelined(wl, step)
@@ -366,7 +445,7 @@ def step_e2e_pipelined(arm, wl, step):
     main.wait_event(wl.cams_copied[buf])
     pairs = (arm._rasterizer(wl.cam_all[buf][v]) for v in range(wl.vpr))  # built lazily, view by view
     total = None
-    with wl.flat.direct():
+    with wl.flat.direct(overwrite=True):
         for v, (color, normal, depth, opac, _) in enumerate(iter_view_pairs(pairs)):
             slot = v & 1
             if v + 1 < wl.vpr:
@@ -421,43 +500,49 @@ def timed(fn, arm, wl, steps, warmup, world, device):
     return max_over_ranks(e0.elapsed_time(e1), world, device)
 
 
-def scene_stats(wl):
-    """Measured P_visible and num_rendered per camera (outside any timed region)."""
-    from diff_gaussian_rasterization import _C
-    e = torch.Tensor([])
-    p = wl.params
-    Pv, R = [], []
-    for cam in wl.cam_dev:
-        out = _C.rasterize_gaussians(
-            wl.bg, p["means3D"].detach(), p["colors_precomp"].detach() if "colors_precomp" in p else e,
-            p["opacities"].detach(), p["scales"].detach(), p["rotations"].detach(), 1.0, e,
-            cam[0:16].view(4, 4), cam[16:32].view(4, 4), wl.prcppoint, wl.patch_bbox, wl.tanfovx,
-            wl.tanfovy, wl.H, wl.W, p["shs"].detach() if "shs" in p else e, wl.deg, cam[32:35],
-            False, False, False, False, wl.config)
-        R.append(int(out[0]))
-        Pv.append(int((out[5] > 0).sum().item()))
-    return sum(Pv) / len(Pv), sum(R) / len(R)
+def scene_stats(wl, arm):
+    """Measured P_visible and num_rendered, averaged over this rank's cameras (outside any timed
+    region; each arm measures with its own rasterizer, so the reference arm never loads the product)."""
+    st = [arm.stats(cam) for cam in wl.cam_dev]
+    return sum(a for a, _ in st) / len(st), sum(b for _, b in st) / len(st)
 
 
 def algorithmic_bytes(wl, Pv, R):
-    """Per-launch algorithmic bytes of every kernel."""
+    """Algorithmic bytes per FRAME of every kernel id, by the repo's own accounting,
+    and how many launches of that id a frame has. The depth presort moves the P depth keys (4 passes of
+    8-byte pairs in and out), the tile sort the R pairs (tile_passes passes)."""
     P, Npix = wl.P, wl.W * wl.H
     T = ((wl.W + 15) // 16) * ((wl.H + 15) // 16)
     M = (wl.deg + 1) ** 2 if "shs" in wl.params else 0
     Cin = 44 + 12 * M if M else 56
     G = Cin + 12
+    tile_bits = max(1, T.bit_length())
+    tile_passes = (tile_bits + 7) // 8
     return {
-        "preprocess_fwd": P * (Cin + 4) + Pv * 92,
-        "scan_lookback": P * 8,
-        "duplicate_keys": Pv * 20 + R * 12,
-        "radix_hist": R * 8,
-        "radix_hist_scan": 0,
-        "radix_onesweep": R * 24,
-        "tile_ranges": R * 8 + T * 8,
-        "blend_fwd": R * (4 + 92) + Npix * 44,
-        "blend_bwd": R * (4 + 92) + Npix * 44 + Pv * 52,
-        "geom_bwd": Pv * 52 + P * Cin + P * G,
+        "preprocess_fwd": (P * (Cin + 4) + Pv * 92, 1),
+        "radix_hist": (P * 4, 1),
+        "radix_onesweep": (4 * P * 16 + tile_passes * R * 16, 4 + tile_passes),
+        "scan_lookback": (P * 12, 1),
+        "duplicate_keys": (Pv * 20 + R * 8, 1),
+        "tile_ranges": (R * 4 + T * 8, 1),
+        "blend_fwd": (R * (4 + 92) + Npix * 44, 1),
+        "blend_bwd": (R * (4 + 92) + Npix * 44 + Pv * 52, 1),
+        "geom_bwd": (Pv * 52 + P * Cin + P * G, 1),
     }
+
+
+def frame_bytes_survey(wl, Pv, R):
+    """SURVEY.md §8(d)'s algorithmic bytes per frame — the REFERENCE algorithm's traffic (64-bit keys,
+    k byte-passes of 24 B), the figure `frame_frac_of_hbm_roofline` is quoted on."""
+    P, Npix = wl.P, wl.W * wl.H
+    T = ((wl.W + 15) // 16) * ((wl.H + 15) // 16)
+    M = (wl.deg + 1) ** 2 if "shs" in wl.params else 0
+    Cin = 44 + 12 * M if M else 56
+    G = Cin + 12
+    k = (32 + max(1, T.bit_length()) + 7) // 8
+    fwd = P * (Cin + 4) + Pv * 92 + R * 12 + R * (8 + k * 24) + R * 8 + T * 8 + R * (4 + 92) + Npix * 44
+    bwd = R * (4 + 92) + Npix * 44 + Pv * 52 * 2 + P * Cin + P * G
+    return fwd + bwd
 
 
 def profile_pass(arm, wl, steps):
@@ -753,6 +838,230 @@ def c5_report(device, N=2_000_000, W=1920, H=1080, iters=5):
             "kernel_ms_per_step": kern, "kernel_ms_sum": round(sum(kern.values()), 3)}
 
 
+def gpu_baselines(device):
+    """BASELINE.md §2's two GPU baselines, on this same B200 (test infrastructure only: oracle/_ref and
+    oracle/): B-GPU-KNN = the UNMODIFIED reference distCUDA2 (KNN/simple_knn.cu:186-222 through
+    oracle/ref_cuda/ref_knn_capi.cu) against ours at 100k / 500k / 2M avatar points, results compared
+    bit for bit; B-GPU-LBS = the reference's torch LBS chain on CUDA tensors (oracle/lbs_oracle.py, with
+    pytorch3d.knn_points — absent offline — restated as chunked cdist + topk) against ours at 100k."""
+    import refdgr
+    from simple_knn._C import distCUDA2
+    from soar_b200 import synthetic
+    out = {}
+    m = synthetic.smplx_template(NB=10, seed=0)
+
+    def wall(fn, reps):
+        fn()
+        torch.cuda.synchronize(device)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            r = fn()
+        torch.cuda.synchronize(device)
+        return (time.perf_counter() - t0) / reps * 1e3, r
+
+    knn = {}
+    if refdgr.available():
+        for n in (100_000, 500_000, 2_000_000):
+            pts = synthetic.avatar_gaussians(n, m["v_template"], seed=0)["points"].to(device)
+            ours_ms, d_ours = wall(lambda: distCUDA2(pts), 5)
+            ref_ms, d_ref = wall(lambda: refdgr.ref_dist2(pts), 3)
+            knn[str(n)] = {"ours_ms": round(ours_ms, 4), "reference_ms": round(ref_ms, 4),
+                           "speedup": round(ref_ms / ours_ms, 2), "bit_identical": bool(torch.equal(d_ours, d_ref))}
+    out["knn"] = {"what": "distCUDA2 on avatar-distributed points: ours vs the unmodified reference CUDA "
+                          "(thrust sort + its boxMeanDist kernel) on the same B200, wall clock around a "
+                          "synchronised call", "points": knn}
+    try:
+        from oracle import lbs_oracle
+        from soar_b200.lbs import SkinWeightQuery, skin_gaussians
+        from soar_b200.smplx_fwd import SmplxPoser
+        n = 100_000
+        pose = synthetic.smplx_pose(NB=10, seed=0)
+        gen = torch.Generator().manual_seed(7)
+        V = m["v_template"].shape[0]
+        pts = (m["v_template"][torch.randint(0, V, (n,), generator=gen)] + 0.002 * torch.randn(n, 3, generator=gen)).to(device)
+        quats = torch.nn.functional.normalize(torch.randn(n, 4, generator=gen), dim=1).to(device)
+        md = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in m.items()}
+        pd = {k: v.to(device) for k, v in pose.items()}
+        keys = ("v_template", "shapedirs", "posedirs", "J_regressor", "parents", "lbs_weights")
+        poser = SmplxPoser(*(md[k] for k in keys))
+        _, _, A0, _ = poser(pd["betas"], torch.zeros(165, device=device), None, None, want_verts=False)
+        inv = torch.linalg.inv(A0)
+        query = SkinWeightQuery(md["v_template"], md["lbs_weights"])
+
+        def ours():
+            _, _, _, bones = poser(pd["betas"], pd["full_pose"], pd["transl"], inv, want_verts=False)
+            return skin_gaussians(pts, quats, query(pts), bones, swizzle=True)
+
+        ours_ms, o = wall(ours, 10)
+        ref_ms, r = wall(lambda: lbs_oracle.lbs_stage_cpu(md, pd, inv, pts, quats), 3)
+        out["lbs"] = {"what": f"c1 on the GPU: SMPL-X forward + 30-NN skin-weight query + bone blend + skinning "
+                              f"of {n} Gaussians; ours vs the reference's torch op chain on the same B200 "
+                              "(knn_points restated as chunked cdist + topk)",
+                      "ours_ms": round(ours_ms, 4), "torch_chain_same_gpu_ms": round(ref_ms, 3),
+                      "torch_chain_split_ms": {k: round(v, 3) for k, v in r[2].items()},
+                      "speedup": round(ref_ms / ours_ms, 1),
+                      "max_abs_points": float((o[0] - r[0]).abs().max())}
+    except Exception as ex:  # noqa: BLE001
+        out["lbs"] = {"error": str(ex)}
+    return out
+
+
+def verify_allreduce(arm, wl, world, rank, device):
+    """Outside the timed region, once: the all-reduced flat buffer must equal the sum of every rank's
+    local (pre-collective) buffer, gathered to rank 0 and summed in float64 (<= 1e-5 relative)."""
+    if world == 1:
+        return None
+    step_resident(arm, wl, 7, allreduce=False)
+    local = wl.flat.flat.clone()
+    parts = [torch.empty_like(local) for _ in range(world)] if rank == 0 else None
+    dist.gather(local, parts, dst=0)
+    wl.flat.allreduce()
+    ok, err = True, 0.0
+    if rank == 0:
+        want = torch.zeros_like(local, dtype=torch.float64)
+        for p_ in parts:
+            want += p_.double()
+        err = float((wl.flat.flat.double() - want).abs().max() / want.abs().max().clamp_min(1e-30))
+        ok = err <= 1e-5 and bool(torch.isfinite(wl.flat.flat).all())
+    flag = torch.tensor([1 if ok else 0], device=device)
+    dist.broadcast(flag, 0)
+    if not int(flag.item()):
+        raise SystemExit(f"allreduce verification FAILED (relative error {err:.3e})")
+    return {"allreduce_verified": True, "max_rel_err": err, "ranks": world, "bytes": wl.flat.nbytes()}
+
+
+# ----------------------------------------------------------------------------------------------
+# BASELINE configs[4]: the dance_0-shaped step, frames sharded over the ranks (weak scaling)
+# ----------------------------------------------------------------------------------------------
+class AvatarWorkload:
+    """One training step of the per-frame (gt) branch of the reference loop
+    (TS/renderer/gaussian_batch_renderer.py:105-181): every rank takes ONE video frame (its own SMPL-X
+    pose) and renders its three gt views — rgb, front normal, back normal (render_front=False) — through
+    soar_b200.avatar.AvatarRenderer, backward to the canonical Gaussians; distCUDA2 of the canonical
+    cloud (the densify re-initialisation, TS/geometry/surfel_base.py:499-503) runs in the step as
+    BASELINE.json lists it; ONE all-reduce of the canonical gradients (points 3, rotation 4, colour 3,
+    in-plane scale 1 floats per Gaussian). Gaussians replicated, frames sharded: no other collective."""
+
+    def __init__(self, device, rank, world, N=2_000_000, W=1920, H=1080):
+        import math as _m
+        from soar_b200 import synthetic
+        from soar_b200.avatar import AvatarCamera, AvatarRenderer
+        from soar_b200.smplx_fwd import SmplxPoser
+        from soar_b200.views import FlatGrads
+        self.N, self.W, self.H, self.device, self.rank, self.world = N, W, H, device, rank, world
+        m = synthetic.smplx_template(NB=10, seed=0)
+        keys = ("v_template", "shapedirs", "posedirs", "J_regressor", "parents", "lbs_weights")
+        poser = SmplxPoser(*(m[k].to(device) for k in keys))
+        ps0 = {k: v.to(device) for k, v in synthetic.smplx_pose(NB=10, seed=0).items()}
+        cano, _, A0, _ = poser(ps0["betas"], torch.zeros_like(ps0["full_pose"]), None)
+        self.ar = AvatarRenderer(poser, cano, torch.linalg.inv(A0))
+        g = {k: v.to(device) for k, v in synthetic.avatar_gaussians(N, cano.cpu(), seed=0).items()}
+        self.g = g
+        # this rank's frame: its own pose (same shape parameters)
+        self.pose = {k: v.to(device) for k, v in synthetic.smplx_pose(NB=10, seed=100 + rank).items()}
+        self.pose["betas"] = ps0["betas"]
+        self.cams = []
+        for c in synthetic.ring_cameras(3 * world, W, H, seed=0, dist=(1.6, 2.0))[3 * rank:3 * rank + 3]:
+            self.cams.append(AvatarCamera(2 * _m.atan(c["tanfovx"]), 2 * _m.atan(c["tanfovy"]), W, H,
+                                          c["viewmatrix"].to(device), c["projmatrix"].to(device),
+                                          c["campos"].to(device), torch.tensor([0.5, 0.5], device=device)))
+        self.params = dict(points=g["points"].requires_grad_(True), rot=g["rot"].requires_grad_(True),
+                           colors=g["colors"].requires_grad_(True),
+                           scale2d=torch.full((N, 1), 0.004, device=device).requires_grad_(True))
+        self.flat = FlatGrads(self.params)
+        self.bg = torch.zeros(3, device=device)
+        gen = torch.Generator(device).manual_seed(rank)
+        self.cot = {k: torch.randn(ch, H, W, device=device, generator=gen) for k, ch in
+                    (("render", 3), ("normal", 3), ("depth", 1), ("mask", 1), ("curv", 1), ("pred_normal", 3))}
+        self.visible = None
+
+    def step(self, allreduce=True):
+        from simple_knn._C import distCUDA2
+        p = self.params
+        self.flat.zero_()
+        d2 = distCUDA2(p["points"].detach())   # densify re-initialisation input; result kept alive
+        self.d2 = d2
+        bones = self.ar.pose(self.pose["betas"], self.pose["full_pose"], self.pose["transl"])
+        w = self.ar.weights(p["points"])
+        for v, cam in enumerate(self.cams):
+            out = self.ar.render(p["points"], p["rot"], w, bones, p["colors"], p["scale2d"], self.g["occ"],
+                                 cam, self.bg, render_front=(v != 2))
+            sum((out[k] * self.cot[k]).sum() for k in self.cot).backward()
+            self.visible = out["visibility_filter"]
+        if allreduce:
+            self.flat.allreduce()
+
+
+def run_c5(args, world, rank, local, device):
+    from soar_b200 import _capi
+    lib = _capi.load()
+    wl = AvatarWorkload(device, rank, world)
+    for _ in range(max(args.warmup, 3)):
+        wl.step()
+    verified = None
+    if world > 1:
+        wl.step(allreduce=False)
+        localbuf = wl.flat.flat.clone()
+        parts = [torch.empty_like(localbuf) for _ in range(world)] if rank == 0 else None
+        dist.gather(localbuf, parts, dst=0)
+        wl.flat.allreduce()
+        if rank == 0:
+            want = sum(p_.double() for p_ in parts)
+            err = float((wl.flat.flat.double() - want).abs().max() / want.abs().max().clamp_min(1e-30))
+            assert err <= 1e-5, f"c5 allreduce verification failed: {err:.3e}"
+            verified = {"allreduce_verified": True, "max_rel_err": err, "ranks": world, "bytes": wl.flat.nbytes()}
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    barrier(world)
+    n0 = lib.soar_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        wl.step()
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    launches = int(lib.soar_launch_count() - n0)
+    clk = clocks.stop() if rank == 0 else None
+    # the collective alone (the flat buffer as it stands), for the share of the step
+    ar_ms = None
+    if world > 1:
+        barrier(world)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(10):
+            wl.flat.allreduce()
+        a1.record()
+        barrier(world)
+        ar_ms = max_over_ranks(a0.elapsed_time(a1), world, device) / 10
+    # per-kernel sums of one more step
+    lib.soar_prof_enable(1)
+    wl.step(allreduce=False)
+    n = 256
+    counts, kms = (ctypes.c_int32 * n)(), (ctypes.c_float * n)()
+    k = lib.soar_prof_summary(n, counts, kms)
+    kern = {lib.soar_kernel_name(i).decode(): round(kms[i], 4) for i in range(k) if counts[i]}
+    lib.soar_prof_enable(0)
+    if rank == 0:
+        views = 3 * world * args.steps
+        line = {"metric": "splat fwd+bwd frames/sec", "value": views / (ms / 1e3), "unit": "frames/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "soar",
+                "config": {"workload": "c5: " + WORKLOADS["c5"]["text"], "views_per_rank_per_step": 3,
+                           "global_views_per_step": 3 * world,
+                           "parallelism": (f"frame-sharded x{world}, 1 allreduce of {wl.flat.nbytes()} B/step"
+                                           if world > 1 else "single GPU"),
+                           "visible_fraction": float(wl.visible.float().mean()),
+                           "l2": "2M Gaussians x (canonical + skinned + records) >> 126 MB L2"},
+                "clocks": clk, "e2e": None, "gpu_launches": launches,
+                "allreduce": verified, "allreduce_ms": ar_ms,
+                "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
+                "kernel_ms_per_step": kern, "kernel_ms_sum": round(sum(kern.values()), 3)}
+        print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -765,33 +1074,74 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the render path has no CPU fallback")
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
+    soar = args.impl == "soar"
 
-    wl = Workload(args.workload, device, rank, world, args.views_per_rank)
+    if args.workload == "c5":
+        if not soar:
+            if rank == 0:
+                print(json.dumps({"impl": "reference", "unavailable":
+                                  "c5 runs the whole avatar chain; the reference's needs pytorch3d / tinycudann / "
+                                  "SMPL-X assets (absent offline). Its rasterizer stage is the c3 / c4 reference arm."}))
+        else:
+            run_c5(args, world, rank, local, device)
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    wl = Workload(args.workload, device, rank, world, args.views_per_rank, float_targets=args.float_targets)
     wl.pipelined = not args.sequential
-    arm = SoarArm(wl) if args.impl == "soar" else ReferenceArm(wl)
-    Pv, R = scene_stats(wl)
-    from soar_b200 import _capi
-    lib = _capi.load()
+    arm = SoarArm(wl) if soar else ReferenceArm(wl)
+    Pv, R = scene_stats(wl, arm)
+    lib = None
+    if soar:   # the reference arm never loads the product library
+        from soar_b200 import _capi
+        lib = _capi.load()
+
+    verified = verify_allreduce(arm, wl, world, rank, device)
 
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    n0 = lib.soar_launch_count()
+    n0 = lib.soar_launch_count() if soar else 0
     ms = timed(step_resident, arm, wl, args.steps, args.warmup, world, device)
-    launches = int(lib.soar_launch_count() - n0)
+    launches = int(lib.soar_launch_count() - n0) if soar else None
     clk = clocks.stop() if rank == 0 else None
-    frames = args.steps * wl.vpr * world
+    frames = args.steps * wl.views_per_step
     value = frames / (ms / 1e3)
+
+    # the collective alone, for its share of the step
+    ar_ms = None
+    if world > 1:
+        barrier(world)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(10):
+            wl.flat.allreduce()
+        a1.record()
+        barrier(world)
+        ar_ms = max_over_ranks(a0.elapsed_time(a1), world, device) / 10
 
     e2e = None
     if not args.no_e2e:
         ms_e = timed(step_e2e, arm, wl, args.steps, max(3, args.warmup // 2), world, device)
         e2e = {"value": frames / (ms_e / 1e3), "unit": "frames/s",
                "h2d_bytes_per_step": wl.h2d_bytes_per_step(), "d2h_bytes_per_step": 4,
-               "ms_per_step": ms_e / args.steps}
+               "ms_per_step": ms_e / args.steps,
+               "targets": "float32" if args.float_targets else
+                          "uint8 (image bytes, converted to [0,1] on the device; both arms)"}
+
+    # the unchanged caller: one blocking GaussianRasterizer call per view, autograd accumulation
+    sequential = None
+    if soar and wl.pipelined and not args.no_sequential:
+        wl.pipelined = False
+        ms_s = timed(step_resident, arm, wl, args.steps, max(3, args.warmup // 2), world, device)
+        wl.pipelined = True
+        sequential = {"value": frames / (ms_s / 1e3), "unit": "frames/s", "ms_per_step": ms_s / args.steps,
+                      "what": "the reference's own call pattern (no begin(), no FlatGrads.direct): one blocking "
+                              "forward + backward per view, autograd accumulates .grad"}
 
     roofline, shares = None, None
-    if args.impl == "soar":
+    if soar:
         prof = profile_pass(arm, wl, min(args.steps, 10))
         tot = sum(t for _, t in prof.values())
         alg = algorithmic_bytes(wl, Pv, R)
@@ -803,7 +1153,13 @@ def main():
             with open(pk) as f:
                 peak = float(json.load(f).get("hbm_gbs", peak))
             peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)"
-        ach = alg.get(top, 0) / (t / cnt * 1e-3) / 1e9
+
+        def gbps(name, launches_, ms_total):
+            """frames profiled x bytes per frame / time of all this id's launches"""
+            b, per_frame = alg.get(name, (0, 1))
+            return (launches_ / per_frame) * b / (ms_total * 1e-3) / 1e9 if ms_total > 0 else None
+
+        ach = gbps(top, cnt, t)
         traffic, traffic_src = None, None
         if args.workload == "c3":  # measured DRAM bytes per launch from the committed ncu capture
             import glob
@@ -813,54 +1169,53 @@ def main():
                     td = json.load(f)
                 traffic = td.get("bytes_per_launch", {}).get(top)
                 traffic_src = os.path.basename(tj[-1])
+        b_top, per_frame_top = alg.get(top, (0, 1))
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
-                    "algorithmic_bytes": alg.get(top, 0), "avg_ms": t / cnt, "launches": cnt,
+                    "algorithmic_bytes": b_top / per_frame_top, "avg_ms": t / cnt, "launches": cnt,
                     "peak_source": peak_src}
         shares = {k: {"launches": c, "ms": round(tt, 4), "share": round(tt / tot, 4),
-                      "GBps": round(alg.get(k, 0) / (tt / c * 1e-3) / 1e9, 1) if tt > 0 else None}
+                      "GBps": round(gbps(k, c, tt), 1) if k in alg and tt > 0 else None}
                   for k, (c, tt) in sorted(prof.items(), key=lambda kv: -kv[1][1])}
-        alg_frame = sum(alg[k] * (6 if k == "radix_onesweep" else 1) for k in alg)
+        alg_frame = frame_bytes_survey(wl, Pv, R)
         roofline["frame_algorithmic_bytes"] = alg_frame
+        roofline["frame_algorithmic_bytes_source"] = "SURVEY.md 8(d) formula (the reference algorithm's traffic)"
+        roofline["frame_bytes_own_kernels"] = sum(b for b, _ in alg.values())
         roofline["frame_frac_of_hbm_roofline"] = (alg_frame * value / world) / (peak * 1e9)
 
-    cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.impl == "soar":
-        cpu = cpu_baseline(wl)
-
-    lbs = None
-    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
-        lbs = lbs_report(device, cpu=not args.no_cpu_baseline)
-
-    post = None
-    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
-        post = postops_report(device, wl.W, wl.H, cpu=not args.no_cpu_baseline)
-
-    c5 = dens = None
-    if rank == 0 and world == 1 and args.impl == "soar" and not args.no_lbs:
-        c5 = c5_report(device)
-        dens = densify_report(device)
+    extras = soar and rank == 0 and world == 1 and args.workload == "c3"
+    cpu = cpu_baseline(wl) if extras and not args.no_cpu_baseline else None
+    lbs = lbs_report(device, cpu=not args.no_cpu_baseline) if extras and not args.no_lbs else None
+    post = postops_report(device, wl.W, wl.H, cpu=not args.no_cpu_baseline) if extras and not args.no_lbs else None
+    c5 = c5_report(device) if extras and not args.no_lbs else None
+    dens = densify_report(device) if extras and not args.no_lbs else None
+    gpub = gpu_baselines(device) if extras and not args.no_gpu_baselines else None
 
     if rank == 0:
+        par = "single GPU"
+        if world > 1:
+            par = f"view-sharded x{world}, 1 allreduce of {wl.flat.nbytes()} B/step"
         line = {
             "metric": "splat fwd+bwd frames/sec", "value": value, "unit": "frames/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "higher_is_better": True, "scaling": wl.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": args.impl,
-            "config": {"workload": f"{args.workload}: single-view rasterizer fwd+bwd, {wl.W}x{wl.H}, "
-                                   f"{wl.P} Gaussians, SH degree {wl.deg}",
-                       "views_per_rank_per_step": wl.vpr, "global_views_per_step": wl.vpr * world,
-                       "parallelism": f"view-sharded x{world}, 1 allreduce of {wl.flat.nbytes()} B/step" if world > 1 else "single GPU",
-                       "view_loop": ("phase 1 of all views of a step enqueued up front "
-                                     "(soar_b200.views.iter_views) + in-place gradient accumulation "
-                                     "(FlatGrads.direct)") if (wl.pipelined and args.impl == "soar")
-                       else "one blocking forward+backward per view, autograd gradient accumulation",
-                       "P_visible": Pv, "num_rendered": R,
-                       "l2": "inputs (>=118 MB params + per-view scratch) exceed the 126 MB L2; cameras cycle"},
-            "clocks": clk, "e2e": e2e, "gpu_launches": launches if args.impl == "soar" else None,
-            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "lbs": lbs, "postops": post, "c5_step": c5, "densify": dens,
+            "config": {"workload": f"{args.workload}: {wl.spec['text']}",
+                       "views_per_rank_per_step": wl.vpr, "global_views_per_step": wl.views_per_step,
+                       "parallelism": par, "P_visible": Pv, "num_rendered": R,
+                       "l2": "inputs (parameters + per-view scratch) exceed the 126 MB L2; cameras cycle"
+                             if args.workload == "c3" else "cameras cycle; every view re-reads parameters and "
+                             "writes fresh scratch (working set per step > 126 MB L2)"},
+            "view_loop": ("phase 1 of all views of a step enqueued up front (soar_b200.views.iter_views) + "
+                          "in-place gradient accumulation (FlatGrads.direct, first view stores)")
+            if (wl.pipelined and soar) else "one blocking forward+backward per view, gradients accumulated with add_",
+            "clocks": clk, "e2e": e2e, "sequential": sequential, "gpu_launches": launches,
+            "allreduce": verified, "allreduce_ms": ar_ms,
+            "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
+            "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "gpu_baselines": gpub, "lbs": lbs,
+            "postops": post, "c5_step": c5, "densify": dens,
         }
-        if args.impl == "reference":
+        if not soar:
             line["cpu_baseline"] = {"value": value, "unit": "frames/s", "cores": 0, "kind": "reference",
                                     "sample": "the reference has no CPU rasterizer: its unmodified CUDA code "
                                               "(oracle/_ref/libref_dgr.so) on the same B200, same workload"}

@@ -13,6 +13,7 @@ with zeros — and launches go to torch's current stream instead of the legacy
 default stream.
 """
 import ctypes
+import threading
 
 import torch
 
@@ -35,9 +36,34 @@ def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+def _config_flags(config):
+    """SoarRastView.config_host_flags for a config tensor. The reference's config lives on the device
+    (pc.config, TS/renderer/diff_gaussian_rasterizer.py:200); its four flags are read back ONCE per
+    tensor object and version counter and remembered on the tensor itself, so the launchers can pick
+    the specialised blend kernels on the host. Anything that cannot be tracked that way (None, a
+    tensor that refuses attributes) reports 'unknown' and the kernels branch on the device copy."""
+    if config is None or config.numel() < 4:
+        return 0
+    ver = config._version
+    hit = getattr(config, "_soar_cfg", None)
+    if hit is not None and hit[0] == ver and hit[1] == config.data_ptr():
+        return hit[2]
+    c = config.detach().reshape(-1)[:4].float().cpu()  # one small blocking read per config tensor
+    flags = _capi.CFG_KNOWN
+    for bit, v in zip((_capi.CFG_SURFACE, _capi.CFG_NORMALIZE_DEPTH, _capi.CFG_PERPIX_DEPTH,
+                       _capi.CFG_LRN_CAM), c.tolist()):
+        if v > 0:
+            flags |= bit
+    try:
+        config._soar_cfg = (ver, config.data_ptr(), flags)
+    except Exception:  # noqa: BLE001
+        return 0
+    return flags
+
+
 def _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered, render_front,
           sort_descending, debug, bg, means3D, sh, colors, opacity, scales, rotations, cov3D,
-          viewmatrix, projmatrix, prcppoint, patchbbox, campos, config):
+          viewmatrix, projmatrix, prcppoint, patchbbox, campos, config, config_flags=0):
     v = _capi.SoarRastView()
     v.P, v.sh_degree, v.M, v.width, v.height = P, int(degree), M, W, H
     v.tanfovx, v.tanfovy, v.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
@@ -48,20 +74,27 @@ def _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered, r
     v.opacities, v.scales, v.rotations, v.cov3D_precomp = p(opacity), p(scales), p(rotations), p(cov3D)
     v.viewmatrix, v.projmatrix, v.prcppoint = p(viewmatrix), p(projmatrix), p(prcppoint)
     v.patch_bbox, v.campos, v.config = p(patchbbox), p(campos), p(config)
+    v.config_host_flags = config_flags
     return v
 
 
 class _PinnedStatus:
-    """Pool of page-locked 2-word host buffers for the asynchronous num_rendered read-back."""
+    """Pool of page-locked 2-word host buffers for the asynchronous num_rendered read-back
+    (shared by all threads, hence the lock)."""
     _free = []
+    _lock = threading.Lock()
 
     @classmethod
     def get(cls):
-        return cls._free.pop() if cls._free else torch.zeros(2, dtype=torch.int32).pin_memory()
+        with cls._lock:
+            if cls._free:
+                return cls._free.pop()
+        return torch.zeros(2, dtype=torch.int32).pin_memory()
 
     @classmethod
     def put(cls, t):
-        cls._free.append(t)
+        with cls._lock:
+            cls._free.append(t)
 
 
 class PendingRaster:
@@ -93,6 +126,7 @@ def rasterize_gaussians_begin(background, means3D, colors, opacity, scales, rota
     rotations, cov3D_precomp = _f32(rotations, "rotations"), _f32(cov3D_precomp, "cov3D_precomp")
     background, viewmatrix = _f32(background, "bg"), _f32(viewmatrix, "viewmatrix")
     projmatrix, prcppoint = _f32(projmatrix, "projmatrix"), _f32(prcppoint, "prcppoint")
+    cfg_flags = _config_flags(config)
     patchbbox, campos, config = _f32(patchbbox, "patch_bbox"), _f32(campos, "campos"), _f32(config, "config")
     M = sh.size(1) if sh is not None else 0
 
@@ -100,7 +134,7 @@ def rasterize_gaussians_begin(background, means3D, colors, opacity, scales, rota
         pend.view = _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, prefiltered,
                           render_front, sort_descending, debug, background, means3D, sh, colors,
                           opacity, scales, rotations, cov3D_precomp, viewmatrix, projmatrix,
-                          prcppoint, patchbbox, campos, config)
+                          prcppoint, patchbbox, campos, config, cfg_flags)
         # the view struct holds raw pointers: keep the (possibly converted) tensors alive
         pend.keep = (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
                      viewmatrix, projmatrix, prcppoint, patchbbox, campos, config)
@@ -173,7 +207,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                  scale_modifier, cov3D_precomp, viewmatrix, projmatrix, prcppoint,
                                  patchbbox, tan_fovx, tan_fovy, dL_dout_color, dL_dout_normal,
                                  dL_dout_depth, dL_dout_opac, sh, degree, campos, geomBuffer, R,
-                                 binningBuffer, imageBuffer, debug, config, accumulate=None):
+                                 binningBuffer, imageBuffer, debug, config, accumulate=None,
+                                 accumulate_store=False):
     """Backward. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations, dL_dviewmat, dL_dprojmat, dL_dcampos) like
     RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187).
@@ -181,7 +216,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     Extension: `accumulate` maps any of "means3D", "colors", "opacity", "sh", "scales",
     "rotations", "cov3D" to a caller-owned float32 buffer of the gradient's shape; this view's
     gradient is then ADDED to it in place (SoarRastGrads.accumulate_mask) and the buffer itself
-    is returned in the tuple."""
+    is returned in the tuple. With `accumulate_store=True` the buffers are OVERWRITTEN instead (every
+    element, zeros for culled Gaussians): the first view of a step needs no zero-fill before it."""
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     dev = means3D.device
@@ -198,7 +234,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             if buf.dtype != torch.float32 or not buf.is_contiguous() or buf.numel() != P * (
                     shape[1] if len(shape) == 2 else shape[1] * shape[2]):
                 raise RuntimeError(f"accumulate[{name!r}] must be a contiguous float32 buffer of shape {shape}")
-            mask |= bit
+            if not accumulate_store:
+                mask |= bit
             return buf
         return (torch.empty if P > 0 else torch.zeros)(shape, **f32)
 
@@ -216,6 +253,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     cov3D_precomp = _f32(cov3D_precomp, "cov3D_precomp")
     background, viewmatrix = _f32(background, "bg"), _f32(viewmatrix, "viewmatrix")
     projmatrix, prcppoint = _f32(projmatrix, "projmatrix"), _f32(prcppoint, "prcppoint")
+    cfg_flags = _config_flags(config)
     patchbbox, campos, config = _f32(patchbbox, "patch_bbox"), _f32(campos, "campos"), _f32(config, "config")
     dL_dout_color, dL_dout_normal = _f32(dL_dout_color, "grad color"), _f32(dL_dout_normal, "grad normal")
     dL_dout_depth, dL_dout_opac = _f32(dL_dout_depth, "grad depth"), _f32(dL_dout_opac, "grad opac")
@@ -225,7 +263,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         # opacities are not needed by the backward (they live in the saved records)
         view = _view(P, M, degree, H, W, tan_fovx, tan_fovy, scale_modifier, False, False, False,
                      debug, background, means3D, sh, colors, None, scales, rotations,
-                     cov3D_precomp, viewmatrix, projmatrix, prcppoint, patchbbox, campos, config)
+                     cov3D_precomp, viewmatrix, projmatrix, prcppoint, patchbbox, campos, config,
+                     cfg_flags)
         grads = _capi.SoarRastGrads()
         grads.dL_dmeans2D, grads.dL_dcolors = g_means2D.data_ptr(), g_colors.data_ptr()
         grads.dL_dopacity, grads.dL_dmeans3D = g_opacity.data_ptr(), g_means3D.data_ptr()

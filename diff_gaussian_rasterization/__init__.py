@@ -75,9 +75,10 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = s
         ctx.num_rendered = num_rendered
         # leaves registered by soar_b200.views.FlatGrads.direct(): accumulate in place in backward
-        ctx.sinks = None
-        from soar_b200.views import _DIRECT, direct_sink
+        ctx.sinks = ctx.direct = None
+        from soar_b200.views import _DIRECT, active_direct, direct_sink
         if _DIRECT:
+            ctx.direct = active_direct()
             sinks = {k: direct_sink(t) for k, t in (("means3D", means3D), ("sh", sh),
                                                     ("colors", colors_precomp), ("opacity", opacities),
                                                     ("scales", scales), ("rotations", rotations),
@@ -98,7 +99,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                 s.tanfovy, grad_out_color, grad_out_normal, grad_out_depth, grad_out_opac, sh,
                 s.sh_degree, s.campos, geom, ctx.num_rendered, binning, img, s.debug, s.config)
         if ctx.sinks:
-            args = args + (ctx.sinks,)
+            args = args + (ctx.sinks, ctx.direct is not None and ctx.direct.first_store())
         (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations, g_view,
          g_proj, g_campos) = _call_with_snapshot(
             _C.rasterize_gaussians_backward, args, s.debug, "snapshot_bw.dump", "backward")
@@ -157,8 +158,15 @@ class GaussianRasterizer(nn.Module):
                 s, means3D.detach(), shs.detach(), colors_precomp.detach(), opacities.detach(),
                 scales.detach(), rotations.detach(), cov3D_precomp.detach(), s.viewmatrix,
                 s.projmatrix, s.campos))
-        self._pending = (pend, means3D.data_ptr(), means3D.shape[0])
+        self._pending = (pend, self._signature(s, means3D, opacities, shs, colors_precomp, scales,
+                                               rotations, cov3D_precomp))
         return self
+
+    @staticmethod
+    def _signature(settings, *tensors):
+        """What begin() rendered from: the settings object and, per tensor argument, storage address,
+        shape and version counter (an in-place update between begin() and forward() bumps it)."""
+        return (id(settings),) + tuple((t.data_ptr(), tuple(t.shape), t._version) for t in tensors)
 
     @staticmethod
     def _normalise(shs, colors_precomp, scales, rotations, cov3D_precomp):
@@ -186,10 +194,12 @@ class GaussianRasterizer(nn.Module):
             shs, colors_precomp, scales, rotations, cov3D_precomp)
         pending = None
         if self._pending is not None:
-            pending, ptr, P = self._pending
+            pending, sig = self._pending
             self._pending = None
-            if ptr != means3D.data_ptr() or P != means3D.shape[0]:
-                raise RuntimeError("GaussianRasterizer.forward: arguments differ from the begin() call")
+            if sig != self._signature(s, means3D, opacities, shs, colors_precomp, scales, rotations,
+                                      cov3D_precomp):
+                raise RuntimeError("GaussianRasterizer.forward: arguments (or raster_settings) differ "
+                                   "from the begin() call, or were modified in place since")
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales,
                                    rotations, cov3D_precomp, s.viewmatrix, s.projmatrix, s.campos, s,
                                    pending)

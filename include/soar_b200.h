@@ -55,7 +55,8 @@ typedef struct SoarRastView {
   const float* colors_precomp; /* [P,3]   or NULL                                */
   const float* opacities;      /* [P]                                            */
   const float* scales;         /* [P,3]   or NULL                                */
-  const float* rotations;      /* [P,4] (w,x,y,z), NOT normalised by the kernel  */
+  const float* rotations;      /* [P,4] (w,x,y,z), NOT normalised by the kernel;
+                                  16-byte aligned -> vector loads, else scalar   */
   const float* cov3D_precomp;  /* [P,6]   or NULL                                */
   const float* viewmatrix;     /* [16]                                           */
   const float* projmatrix;     /* [16]                                           */
@@ -63,7 +64,18 @@ typedef struct SoarRastView {
   const float* patch_bbox;     /* [4] = (h0,w0,h1,w1)                            */
   const float* campos;         /* [3]                                            */
   const float* config;         /* [4] = (surface,normalize_depth,perpix_depth,lrn_cam) */
+  /* Extension: what the HOST knows about `config` (the reference only has the device tensor,
+   * DGR/cuda_rasterizer/forward.cu:464, backward.cu:581). SOAR_CFG_KNOWN set = the other bits equal
+   * `config[i] > 0` and the launchers pick the specialised blend kernels on the host; 0 = unknown, the
+   * kernels branch on the device copy. A set bit that contradicts the device tensor is the caller's
+   * error (the device copy is still what preprocess and the geometry backward read). */
+  uint32_t config_host_flags;
 } SoarRastView;
+#define SOAR_CFG_KNOWN           (1u << 0)
+#define SOAR_CFG_SURFACE         (1u << 1)
+#define SOAR_CFG_NORMALIZE_DEPTH (1u << 2)
+#define SOAR_CFG_PERPIX_DEPTH    (1u << 3)
+#define SOAR_CFG_LRN_CAM         (1u << 4)
 
 /* Gradient outputs of the rasterizer backward: the 11-tuple returned by
  * RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187). The kernels
@@ -77,7 +89,7 @@ typedef struct SoarRastGrads {
   float* dL_dcov3D;     /* [P,6]                                                */
   float* dL_dsh;        /* [P,M,3] (may be NULL when M == 0)                    */
   float* dL_dscales;    /* [P,3]                                                */
-  float* dL_drotations; /* [P,4]                                                */
+  float* dL_drotations; /* [P,4]  (16-byte aligned -> vector stores, else scalar)  */
   float* dL_dviewmat;   /* [16]  nonzero only when config[3] > 0                */
   float* dL_dprojmat;   /* [16]                                                 */
   float* dL_dcampos;    /* [3]                                                  */
@@ -175,7 +187,9 @@ int soar_knn_dist2(const float* points, int32_t P, float* mean_dist2, void* work
  *      TS/utils/smpl.py:613 (weights x bones blend) and
  *      TS/renderer/diff_gaussian_rasterizer.py:103-114 (apply to points/quats)) -- */
 /* weights[N,J] (row-major), bones[J,16] row-major 4x4 (cano->live), points[N,3],
- * quats[N,4] (w,x,y,z). axis_perm: 0 = none (gt views, :138-149),
+ * quats[N,4] (w,x,y,z). quats, out_quats, out_mats, mats and the quaternion gradients are moved as
+ * 16-byte rows: their base pointers must be 16-byte aligned (SOAR_E_INVALID otherwise).
+ * axis_perm: 0 = none (gt views, :138-149),
  * 1 = the SDS-view swizzle (x,y,z)->(z,x,y) of transform_point_cloud("+z,+x,+y"). */
 int soar_lbs_forward(const float* weights, const float* bones, int32_t J, const float* points,
                      const float* quats, int32_t N, int32_t axis_perm, float* out_points,

@@ -67,7 +67,7 @@ def skin(points, quats, weights, bones, swizzle):
     rot_mat = quaternion_to_matrix(quats)
     rot_mat = torch.matmul(mat[..., :3, :3], rot_mat)
     if swizzle:
-        T = torch.zeros(3, 3, dtype=points.dtype)
+        T = torch.zeros(3, 3, dtype=points.dtype, device=points.device)
         T[2, 0] = 1.0  # "+z" -> column 0
         T[0, 1] = 1.0  # "+x" -> column 1
         T[1, 2] = 1.0  # "+y" -> column 2
@@ -79,9 +79,12 @@ def skin(points, quats, weights, bones, swizzle):
 
 
 def query_weights(points, cano_vertices, lbs_weights, K=30):
-    """TS/utils/smpl.py:618-637 with pytorch3d.knn_points restated as cdist + topk."""
+    """TS/utils/smpl.py:618-637 with pytorch3d.knn_points restated as cdist + a stable sort: ties in
+    distance (duplicated vertices) go to the lower vertex index, the rule the golden vectors
+    (tests/golden/make_golden_weights.py) and the product kernels follow."""
     d2 = torch.cdist(points.double(), cano_vertices.double()).pow(2).float()
-    dist, idx = torch.topk(d2, K, dim=1, largest=False)
+    dist, idx = torch.sort(d2, dim=1, stable=True)
+    dist, idx = dist[:, :K], idx[:, :K]
     dist = dist.sqrt().clamp_(0.0001, 1.0)
     w = lbs_weights[idx]
     ws = 1.0 / dist
@@ -98,22 +101,22 @@ def _rodrigues_t(rv):
     rx, ry, rz = d[:, 0:1], d[:, 1:2], d[:, 2:3]
     z = torch.zeros_like(rx)
     K = torch.cat([z, -rz, ry, rz, z, -rx, -ry, rx, z], dim=1).view(-1, 3, 3)
-    return torch.eye(3, dtype=rv.dtype)[None] + s * K + (1 - c) * torch.bmm(K, K)
+    return torch.eye(3, dtype=rv.dtype, device=rv.device)[None] + s * K + (1 - c) * torch.bmm(K, K)
 
 
 def smplx_forward_torch(model, betas, full_pose, transl):
     """lbs() (TS/utils/smplx/lbs.py:147-246) + the transl fold (body_models.py:1380-1383) as the
-    same sequence of torch ops, batch 1, CPU. -> (verts [V,3], A [J,4,4])."""
+    same sequence of torch ops, batch 1, on the tensors' device. -> (verts [V,3], A [J,4,4])."""
     J = model["J_regressor"].shape[0]
     parents = model["parents"].tolist()
     v_shaped = model["v_template"] + torch.einsum("bl,mkl->bmk", betas, model["shapedirs"])[0]
     joints = torch.einsum("ik,ji->jk", v_shaped, model["J_regressor"])
     R = _rodrigues_t(full_pose.view(-1, 3))
-    feat = (R[1:] - torch.eye(3)).reshape(1, -1)
+    feat = (R[1:] - torch.eye(3, device=R.device)).reshape(1, -1)
     v_posed = torch.matmul(feat, model["posedirs"]).view(-1, 3) + v_shaped
     rel = joints.clone()
     rel[1:] -= joints[parents[1:]]
-    T = torch.zeros(J, 4, 4)
+    T = torch.zeros(J, 4, 4, device=R.device)
     T[:, :3, :3], T[:, :3, 3], T[:, 3, 3] = R, rel, 1.0
     chain = [T[0]]
     for i in range(1, J):
@@ -149,15 +152,24 @@ def query_weights_chunked(points, cano_vertices, lbs_weights, K=30, chunk=8192):
 def lbs_stage_cpu(model, pose, inv_mats, points, quats, swizzle=True):
     """One LBS stage as the reference runs it per render (TS/utils/smpl.py:592-613 +
     TS/renderer/diff_gaussian_rasterizer.py:103-114): SMPL-X forward, cano->live bones, skin-weight
-    query, bone blend, skinning of points and quaternions. Returns (points', quats', split_ms)."""
+    query, bone blend, skinning of points and quaternions. Returns (points', quats', split_ms).
+    Device-agnostic: bench.py also runs it on CUDA tensors (the reference's torch chain on the same
+    B200, with pytorch3d.knn_points — absent here — restated as chunked cdist + topk)."""
     import time
-    t0 = time.perf_counter()
+    cuda = points.is_cuda
+
+    def now():
+        if cuda:
+            torch.cuda.synchronize()
+        return time.perf_counter()
+
+    t0 = now()
     _, A = smplx_forward_torch(model, pose["betas"], pose["full_pose"], pose["transl"])
     bones = torch.matmul(A, inv_mats)
-    t1 = time.perf_counter()
+    t1 = now()
     w = query_weights_chunked(points, model["v_template"], model["lbs_weights"])
-    t2 = time.perf_counter()
+    t2 = now()
     p, q, _ = skin(points, quats, w, bones, swizzle)
-    t3 = time.perf_counter()
+    t3 = now()
     return p, q, {"smplx_fwd_ms": (t1 - t0) * 1e3, "weight_query_ms": (t2 - t1) * 1e3,
                   "blend_apply_ms": (t3 - t2) * 1e3}

@@ -44,7 +44,11 @@ class SoarRastView(Structure):
         ("patch_bbox", c_void_p),
         ("campos", c_void_p),
         ("config", c_void_p),
+        ("config_host_flags", c_uint32),
     ]
+
+
+CFG_KNOWN, CFG_SURFACE, CFG_NORMALIZE_DEPTH, CFG_PERPIX_DEPTH, CFG_LRN_CAM = 1, 2, 4, 8, 16
 
 
 class SoarRastGrads(Structure):

@@ -52,6 +52,7 @@ class AvatarRenderer:
         self.query = SkinWeightQuery(cano_vertices, poser.lbs_weights)
         self.inv_mats = inv_mats.detach().to(device=poser.device, dtype=torch.float32).reshape(-1, 4, 4)
         self.config = torch.tensor(config, dtype=torch.float32, device=poser.device)
+        self._full_patch = {}  # (H, W) -> device tensor, built once per image size
 
     # ---- once per pose / per step -------------------------------------------------------------
     def pose(self, betas, full_pose, transl=None):
@@ -63,11 +64,25 @@ class AvatarRenderer:
         return self.query(points)
 
     # ---- once per view ------------------------------------------------------------------------
+    def _patch(self, camera, patch_bbox):
+        if patch_bbox is not None:
+            return patch_bbox
+        key = (int(camera.image_height), int(camera.image_width))
+        if key not in self._full_patch:
+            self._full_patch[key] = camera.full_patch()
+        return self._full_patch[key]
+
     def render(self, points, rot, weights, bones, colors, scale2d, occ, camera: AvatarCamera,
                bg_color, sds_view=False, scaling_modifier=1.0, render_occ=True,
-               screenspace_points: Optional[torch.Tensor] = None):
+               screenspace_points: Optional[torch.Tensor] = None, render_front=True,
+               patch_bbox: Optional[torch.Tensor] = None):
         """points [N,3], rot [N,4] (unnormalised parameter), weights [N,J], bones [J,4,4],
-        colors [N,3], scale2d [N,1] (linear), occ [N,1] in (0,1). Returns the reference's dict."""
+        colors [N,3], scale2d [N,1] (linear), occ [N,1] in (0,1). Returns the reference's dict.
+        render_front: the reference's argument of the same name (default True, :60): the main pass
+        always has the SETTING render_front=False and sorts `descending = not render_front` (:186-187) —
+        front view = ascending depth order; the back-normal pass of gaussian_batch_renderer.py:167
+        passes render_front=False. patch_bbox: (h0, w0, h1, w1) as camera.random_patch() returns it
+        (:182); None = the whole image."""
         rot = torch.nn.functional.normalize(rot, dim=-1)                                  # :74
         means3D, rotations, _ = skin_gaussians(points, rot, weights, bones, swizzle=sds_view)
         if screenspace_points is None:                                                    # :155-164
@@ -80,11 +95,11 @@ class AvatarRenderer:
             image_height=int(camera.image_height), image_width=int(camera.image_width),
             tanfovx=math.tan(camera.FoVx * 0.5), tanfovy=math.tan(camera.FoVy * 0.5), bg=bg_color,
             scale_modifier=scaling_modifier, viewmatrix=camera.world_view_transform,
-            projmatrix=camera.full_proj_transform, patch_bbox=camera.full_patch(),
+            projmatrix=camera.full_proj_transform, patch_bbox=self._patch(camera, patch_bbox),
             prcppoint=camera.prcppoint, sh_degree=0, campos=camera.camera_center, prefiltered=False,
             debug=False, config=self.config)
         rasterizer = GaussianRasterizer(GaussianRasterizationSettings(
-            render_front=False, sort_descending=True, **common))                          # :173-191
+            render_front=False, sort_descending=not render_front, **common))              # :173-191
         scales = scale2d.repeat(1, 3)
         scales[..., -1] = -1e10                                                            # :239 (Q7)
         ones = torch.ones((points.shape[0], 1), dtype=torch.float32, device=points.device)

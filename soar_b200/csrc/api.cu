@@ -237,6 +237,7 @@ int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
   b.out_color = out_color; b.out_normal = out_normal; b.out_depth = out_depth; b.out_opac = out_opac;
   // the ping-pong half the sort left free holds one block-mask byte per list entry
   b.pair_mask = reinterpret_cast<uint8_t*>(keys[sorted ^ 1]);
+  b.cfg_flags = v->config_host_flags;
   return launch_blend_fwd(b, d.grid_y, stream);
 }
 
@@ -293,6 +294,7 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
       b.dL_dpixdepth = dL_dout_depth; b.dL_dpixopac = dL_dout_opac;
       b.gacc = gacc;
       b.pair_mask = reinterpret_cast<const uint8_t*>(at(binning, BL.keys[sorted ^ 1]));
+      b.cfg_flags = v->config_host_flags;
       rc = launch_blend_bwd(b, d.grid_y, stream);
       if (rc) return rc;
     }
@@ -308,6 +310,10 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
   g.rotations = v->rotations; g.cov3D_precomp = v->cov3D_precomp;
   g.viewmatrix = v->viewmatrix; g.projmatrix = v->projmatrix; g.campos = v->campos;
   g.config = v->config; g.gacc = gacc; g.g = *grads;
+  {
+    const int mode = blend_bwd_scalar_mode();
+    g.mean_direct = mode >= 0 && (mode & 4);
+  }
   return launch_geom_bwd(g, stream);
 }
 

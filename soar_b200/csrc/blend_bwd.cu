@@ -143,8 +143,17 @@ struct BlendBwdSmem {
   uint32_t max_contrib[N_BLK];
 };
 
-template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+// MODE selects an arithmetic variant of the scalar twin. The variants exist to ATTRIBUTE the
+// gradient deviation from the reference (tests/test_grad_attribution_gpu.py):
+//   bit 0 (1)  precise expf and IEEE division instead of ex2.approx / rcp.approx
+//   bit 1 (2)  the reference's per-channel accum_rec recurrences and separate T_final terms instead
+//              of the single scalar S recurrence and the fused tf_k constant
+//   bit 2 (4)  dL/dmean2D summed per pixel with the reference's expression
+//              dd * (A dx + B dy), dd * (C dy + B dx) instead of being formed at flush time from the
+//              moments sum(dd dx), sum(dd dy) (BlendBwdArgs.mean_direct tells geom_bwd which it got)
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH, int MODE>
 __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSmem& sm) {
+  constexpr bool PRECISE = MODE & 1, PER_CHANNEL = MODE & 2, MEAN_DIRECT = MODE & 4;
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
   const uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y;
@@ -208,6 +217,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
 
   float T = T_final;
   float S = 0.f, cg_last = 0.f, last_alpha = 0.f;
+  float accum_rec[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, last_ch[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 
   for (int i = 0; i < rounds; i++) {
     // ---- stage (from the back), cull against the tile, compact in walk order ---------
@@ -265,7 +275,7 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
         if (!__any_sync(0xffffffffu, live)) continue;
         // the backward is compared at 1e-3 relative (the reference's own atomics are unordered):
         // single-instruction ex2 / rcp approximations (2^-22 relative) are far inside that
-        const float G = ex2_approx(power * 1.4426950408889634f);
+        const float G = PRECISE ? expf(power) : ex2_approx(power * 1.4426950408889634f);
         float alpha = min(0.99f, q1j.y * G);
         live = live && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, live)) continue;
@@ -279,8 +289,8 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
         for (int k = LS_COUNT; k < 16; ++k) v[k] = 0.f;
         {
           const float T_behind = T;  // transmittance after this Gaussian (front-to-back)
-          const float rcp = rcp_approx(1.f - alpha);
-          T = T * rcp;
+          const float rcp = PRECISE ? 1.f / (1.f - alpha) : rcp_approx(1.f - alpha);
+          T = PRECISE ? T / (1.f - alpha) : T * rcp;
           const float dchannel_dcolor = alpha * T;
           const float4 q2 = sm.q2[j];
 
@@ -311,20 +321,53 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
           }
           cg += d_cur * dL_ddepth_ch;
           v[LS_DD] = dchannel_dcolor * dL_ddepth_ch * 1;
-          S = last_alpha * cg_last + (1.f - last_alpha) * S;
-          cg_last = cg;
-          float dL_dalpha = cg - S;
-          if (NORM_DEPTH) dL_dalpha += norm_k / T_behind;  // = norm_k / ((1-alpha) * T)
-          dL_dalpha *= T;
-          dL_dalpha += tf_k * rcp;
-          last_alpha = alpha;
+          float dL_dalpha;
+          if (!PER_CHANNEL) {
+            S = last_alpha * cg_last + (1.f - last_alpha) * S;
+            cg_last = cg;
+            dL_dalpha = cg - S;
+            if (NORM_DEPTH) dL_dalpha += norm_k / T_behind;  // = norm_k / ((1-alpha) * T)
+            dL_dalpha *= T;
+            dL_dalpha += tf_k * rcp;
+          } else if (live) {
+            // backward.cu:700-790 term by term (skipped contributions leave every recurrence
+            // untouched there, hence the predicate)
+            const float4 q3 = SURFACE ? sm.q3[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float c_cur[7] = {q2.x, q2.y, q2.z, q3.x, q3.y, q3.z, d_cur};
+            const float g_ch[7] = {dL_dpixC[0], dL_dpixC[1], dL_dpixC[2], dL_dpixN[0], dL_dpixN[1],
+                                   dL_dpixN[2], dL_ddepth_ch};
+            dL_dalpha = 0.f;
+#pragma unroll
+            for (int ch = 0; ch < 7; ++ch) {
+              if (!SURFACE && ch >= 3 && ch < 6) continue;
+              accum_rec[ch] = last_alpha * last_ch[ch] + (1.f - last_alpha) * accum_rec[ch];
+              last_ch[ch] = c_cur[ch];
+              float part = 0.f;
+              if (ch == 6 && NORM_DEPTH)
+                part += dL_dpixD * D_final / (1.f - T_final) / (1.f - T_final) * -T_final / (1 - alpha) / T;
+              part += (c_cur[ch] - accum_rec[ch]) * g_ch[ch];
+              dL_dalpha += part;
+            }
+            dL_dalpha *= T;
+            dL_dalpha += dL_dpixO * T_final / (1 - alpha);
+            dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+            if (!NORM_DEPTH) dL_dalpha += (-T_final / (1.f - alpha)) * (10 * dL_dpixD);
+          } else {
+            dL_dalpha = 0.f;
+          }
+          if (!PER_CHANNEL || live) last_alpha = alpha;
 
           const float gda = Gl * dL_dalpha;
           const float dL_ddist = gda * q1j.y * -0.5f;
           const float ddx = dL_ddist * d.x, ddy = dL_ddist * d.y;
           v[LS_DO] = gda;
-          v[LS_MX] = ddx;
-          v[LS_MY] = ddy;
+          if (MEAN_DIRECT) {
+            v[LS_MX] = dL_ddist * (q0j.z * d.x + q0j.w * d.y);
+            v[LS_MY] = dL_ddist * (q1j.x * d.y + q0j.w * d.x);
+          } else {
+            v[LS_MX] = ddx;
+            v[LS_MY] = ddy;
+          }
           v[LS_MXX] = ddx * d.x;
           v[LS_MXY] = ddx * d.y;
           v[LS_MYY] = ddy * d.y;
@@ -598,6 +641,17 @@ __device__ __forceinline__ void blend_bwd2_body(const BlendBwdArgs& a, BlendBwdS
   }
 }
 
+// The product kernel: one instantiation per (surface, per-pixel depth, normalize_depth) combination the
+// reference's config can take, picked on the HOST when the caller knows the flags
+// (SoarRastView.config_host_flags) — each body then gets the whole 64-register budget to itself. The
+// all-in-one kernel below, which branches on the device copy of config (backward.cu:581), serves callers
+// that only hold the device tensor; it spills (the allocator has to cover all six bodies at once).
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+__global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel_t(const BlendBwdArgs a) {
+  __shared__ BlendBwdSmem sm;
+  blend_bwd2_body<SURFACE, DEPTH_DIFF, NORM_DEPTH>(a, sm);
+}
+
 template <bool SURFACE, bool DEPTH_DIFF>
 __device__ __forceinline__ void blend_bwd2_pick(const BlendBwdArgs& a, BlendBwdSmem& sm, bool normalize_depth) {
   if (normalize_depth) blend_bwd2_body<SURFACE, DEPTH_DIFF, true>(a, sm);
@@ -613,30 +667,59 @@ __global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel(const Blend
   else blend_bwd2_pick<false, false>(a, sm, normalize_depth);
 }
 
-// The config flags live in device memory (backward.cu:581): one kernel, specialised bodies
-// selected by a uniform branch.
+// The scalar twin (one pixel per thread), kept for the twin tests and the attribution variants.
+template <int MODE>
 __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdArgs a) {
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;
   if (surface && per_pixel_depth) {
-    if (normalize_depth) blend_bwd_body<true, true, true>(a, sm);
-    else blend_bwd_body<true, true, false>(a, sm);
+    if (normalize_depth) blend_bwd_body<true, true, true, MODE>(a, sm);
+    else blend_bwd_body<true, true, false, MODE>(a, sm);
   } else if (surface) {
-    if (normalize_depth) blend_bwd_body<true, false, true>(a, sm);
-    else blend_bwd_body<true, false, false>(a, sm);
+    if (normalize_depth) blend_bwd_body<true, false, true, MODE>(a, sm);
+    else blend_bwd_body<true, false, false, MODE>(a, sm);
   } else {
-    if (normalize_depth) blend_bwd_body<false, false, true>(a, sm);
-    else blend_bwd_body<false, false, false>(a, sm);
+    if (normalize_depth) blend_bwd_body<false, false, true, MODE>(a, sm);
+    else blend_bwd_body<false, false, false, MODE>(a, sm);
   }
+}
+
+// SOAR_BLEND_BWD_SCALAR=<n>: run the scalar twin; n - 1 = MODE bits (1 -> MODE 0 ... 8 -> MODE 7).
+int blend_bwd_scalar_mode() {
+  const char* e = getenv("SOAR_BLEND_BWD_SCALAR");
+  if (!e) return -1;
+  const int n = atoi(e);
+  return n >= 1 && n <= 8 ? n - 1 : 0;
 }
 
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream) {
   dim3 grid(a.grid_x, grid_y, 1);
   {
     KernelScope ks(K_BLEND_BWD, stream);
-    if (getenv("SOAR_BLEND_BWD_SCALAR")) blend_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(a);
-    else blend_bwd2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(a);
+    const int mode = blend_bwd_scalar_mode();
+    if (mode >= 0) {
+      switch (mode) {
+        case 0: blend_bwd_kernel<0><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 1: blend_bwd_kernel<1><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 2: blend_bwd_kernel<2><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 3: blend_bwd_kernel<3><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 4: blend_bwd_kernel<4><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 5: blend_bwd_kernel<5><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        case 6: blend_bwd_kernel<6><<<grid, TILE_PIX, 0, stream>>>(a); break;
+        default: blend_bwd_kernel<7><<<grid, TILE_PIX, 0, stream>>>(a); break;
+      }
+    } else if (a.cfg_flags & SOAR_CFG_KNOWN) {
+      const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
+                 dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
+#define SOAR_BWD2(S, D, N) blend_bwd2_kernel_t<S, D, N><<<grid, BWD2_THREADS, 0, stream>>>(a)
+      if (dd) { if (norm) SOAR_BWD2(true, true, true); else SOAR_BWD2(true, true, false); }
+      else if (surface) { if (norm) SOAR_BWD2(true, false, true); else SOAR_BWD2(true, false, false); }
+      else { if (norm) SOAR_BWD2(false, false, true); else SOAR_BWD2(false, false, false); }
+#undef SOAR_BWD2
+    } else {
+      blend_bwd2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(a);
+    }
   }
   SOAR_LAUNCH_CHECK("blend_bwd_kernel");
   return SOAR_OK;

@@ -145,6 +145,23 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// ---- 16-byte rows behind caller-owned pointers ------------------------------------------------
+// [P,4] tensors (rotations and their gradient) are moved as float4 when the base pointer is 16-byte
+// aligned — always true for a torch allocation, NOT for a slice of a flat buffer at an odd float
+// offset (FlatGrads slices are padded for that reason). The launchers test the pointers and hand the
+// kernels a uniform flag; the scalar path is the fallback.
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+__device__ __forceinline__ float4 ld_row4(const float* base, size_t row, bool vec) {
+  if (vec) return reinterpret_cast<const float4*>(base)[row];
+  const float* p = base + 4 * row;
+  return make_float4(p[0], p[1], p[2], p[3]);
+}
+__device__ __forceinline__ void st_row4(float* base, size_t row, float4 v, bool vec) {
+  if (vec) { reinterpret_cast<float4*>(base)[row] = v; return; }
+  float* p = base + 4 * row;
+  p[0] = v.x; p[1] = v.y; p[2] = v.z; p[3] = v.w;
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 __device__ __forceinline__ uint32_t lanemask_lt() {
   uint32_t m;

@@ -77,7 +77,7 @@ __device__ __forceinline__ void geom_bwd_body(const GeomBwdArgs& a) {
     const float4* rec = reinterpret_cast<const float4*>(a.records + (size_t)idx * REC_FLOATS);
     r0 = __ldg(rec + 0); r1 = __ldg(rec + 1);
     mean_in = make_float3(a.means3D[3 * idx], a.means3D[3 * idx + 1], a.means3D[3 * idx + 2]);
-    if (a.rotations != nullptr) q_in = reinterpret_cast<const float4*>(a.rotations)[idx];
+    if (a.rotations != nullptr) q_in = ld_row4(a.rotations, idx, a.rot_vec);
     if (a.scales != nullptr)
       scale_in = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
   }
@@ -110,7 +110,7 @@ __device__ __forceinline__ void geom_bwd_body(const GeomBwdArgs& a) {
       for (int i = 0; i < 6; ++i) p[i] = 0.f;
     }
     if (!acc_scl) { p = a.g.dL_dscales + 3 * (size_t)idx;  p[0] = p[1] = p[2] = 0.f; }
-    if (!acc_rot) reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!acc_rot) st_row4(a.g.dL_drotations, idx, make_float4(0.f, 0.f, 0.f, 0.f), a.rot_vec);
     if (a.M > 0 && a.g.dL_dsh && !acc_sh) {
       if (SHV > 0) {
         float4* p4 = reinterpret_cast<float4*>(a.g.dL_dsh + (size_t)idx * SHV * 3);
@@ -139,6 +139,7 @@ __device__ __forceinline__ void geom_bwd_body(const GeomBwdArgs& a) {
     const float ddelx_dx = 0.5 * a.W;
     const float ddely_dy = 0.5 * a.H;
     float2 dL_dmean2d = {2 * (cA * m_x + cB * m_y) * ddelx_dx, 2 * (cC * m_y + cB * m_x) * ddely_dy};
+    if (a.mean_direct) dL_dmean2d = make_float2(2 * m_x * ddelx_dx, 2 * m_y * ddely_dy);
     if (surface && a.config[2] > 0) {
       const float4 r2 = __ldg(rec + 2), r3 = __ldg(rec + 3), r4 = __ldg(rec + 4);
       const float J6 = r2.w, J9 = r3.w, gd = A3.y;
@@ -507,13 +508,18 @@ __device__ __forceinline__ void geom_bwd_body(const GeomBwdArgs& a) {
              2 * z * (G.m[1][2] + G.m[2][1]) - 4 * y * (G.m[2][2] + G.m[0][0]);
       dq.w = 2 * r * (G.m[0][1] - G.m[1][0]) + 2 * x * (G.m[2][0] + G.m[0][2]) +
              2 * y * (G.m[1][2] + G.m[2][1]) - 4 * z * (G.m[1][1] + G.m[0][0]);
-      put4(reinterpret_cast<float4*>(a.g.dL_drotations) + idx, dq, acc_rot);
+      if (a.rot_vec) {
+        put4(reinterpret_cast<float4*>(a.g.dL_drotations) + idx, dq, acc_rot);
+      } else {
+        float* p = a.g.dL_drotations + 4 * (size_t)idx;
+        put(p, dq.x, acc_rot); put(p + 1, dq.y, acc_rot); put(p + 2, dq.z, acc_rot); put(p + 3, dq.w, acc_rot);
+      }
     } else {
       if (!acc_scl) {
         float* p = a.g.dL_dscales + 3 * (size_t)idx;
         p[0] = p[1] = p[2] = 0.f;
       }
-      if (!acc_rot) reinterpret_cast<float4*>(a.g.dL_drotations)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (!acc_rot) st_row4(a.g.dL_drotations, idx, make_float4(0.f, 0.f, 0.f, 0.f), a.rot_vec);
     }
   }
 
@@ -536,7 +542,9 @@ __global__ void __launch_bounds__(GB_THREADS, 4) geom_bwd_kernel(const GeomBwdAr
   else geom_bwd_body<false, SHV>(a);
 }
 
-int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream) {
+int launch_geom_bwd(const GeomBwdArgs& a_in, cudaStream_t stream) {
+  GeomBwdArgs a = a_in;
+  a.rot_vec = aligned16(a.rotations) && aligned16(a.g.dL_drotations);
   // camera gradients are sums: clear them here (the reference gets zeros from torch)
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dviewmat, 0, 16 * sizeof(float), stream));
   SOAR_CUDA_TRY(cudaMemsetAsync(a.g.dL_dprojmat, 0, 16 * sizeof(float), stream));

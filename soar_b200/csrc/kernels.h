@@ -28,6 +28,7 @@ struct PreprocessArgs {
   uint32_t* tiles_touched;
   uint32_t* depth_keys;  // depth bits of visible Gaussians, 0xffffffff for culled ones
   uint32_t* error_flag;
+  int rot_vec;  // rotations is 16-byte aligned (set by the launcher)
 };
 int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream);
 
@@ -60,6 +61,7 @@ struct BlendFwdArgs {
   float* out_depth;
   float* out_opac;
   uint8_t* pair_mask;  // [R] block mask of every staged list entry (read back by the backward)
+  uint32_t cfg_flags;  // SoarRastView.config_host_flags
 };
 int launch_blend_fwd(const BlendFwdArgs& a, int grid_y, cudaStream_t stream);
 
@@ -79,7 +81,10 @@ struct BlendBwdArgs {
   const float* dL_dpixopac;
   float* gacc;
   const uint8_t* pair_mask;  // [R] written by the forward blend of the same view
+  uint32_t cfg_flags;  // SoarRastView.config_host_flags
 };
+// -1: the packed product kernel; >= 0: the scalar twin's MODE bits (SOAR_BLEND_BWD_SCALAR, blend_bwd.cu)
+int blend_bwd_scalar_mode();
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream);
 
 struct GeomBwdArgs {
@@ -97,6 +102,8 @@ struct GeomBwdArgs {
   const float* campos;
   const float* config;
   const float* gacc;
+  int rot_vec;      // rotations and dL_drotations are 16-byte aligned (set by the launcher)
+  int mean_direct;  // GA_MX / GA_MY hold sum(dd (A dx + B dy)), sum(dd (C dy + B dx)) instead of the moments
   SoarRastGrads g;
 };
 int launch_geom_bwd(const GeomBwdArgs& a, cudaStream_t stream);

@@ -310,6 +310,10 @@ int soar_lbs_forward(const float* weights, const float* bones, int32_t J, const 
     set_error("soar_lbs_forward: a required pointer is NULL");
     return SOAR_E_INVALID;
   }
+  if (!aligned16(quats) || !aligned16(out_quats) || (out_mats && !aligned16(out_mats))) {
+    set_error("soar_lbs_forward: quats / out_quats / out_mats must be 16-byte aligned");
+    return SOAR_E_INVALID;
+  }
   const size_t smem = (size_t)(LBS_MAX_J * 12 + LBS_THREADS * J) * sizeof(float);
   const int grid = ceil_div(N, LBS_THREADS);
   {
@@ -329,6 +333,10 @@ int soar_lbs_backward(const float* mats, const float* quats, int32_t N, int32_t 
   if (N == 0) return SOAR_OK;
   if (!mats || !quats || !dL_dout_points || !dL_dout_quats || !dL_dpoints || !dL_dquats) {
     set_error("soar_lbs_backward: a required pointer is NULL");
+    return SOAR_E_INVALID;
+  }
+  if (!aligned16(mats) || !aligned16(quats) || !aligned16(dL_dout_quats) || !aligned16(dL_dquats)) {
+    set_error("soar_lbs_backward: mats / quats / dL_dout_quats / dL_dquats must be 16-byte aligned");
     return SOAR_E_INVALID;
   }
   {

@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
   // the other small per-Gaussian inputs are requested together with the mean, ahead of the culling
   // tests that decide whether they are needed: one DRAM round trip instead of three
   float4 q_in = make_float4(1.f, 0.f, 0.f, 0.f);
-  if (a.rotations != nullptr) q_in = reinterpret_cast<const float4*>(a.rotations)[idx];
+  if (a.rotations != nullptr) q_in = ld_row4(a.rotations, idx, a.rot_vec);
   float3 sc_in = make_float3(0.f, 0.f, 0.f);
   if (a.cov3D_precomp == nullptr)
     sc_in = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
@@ -164,8 +164,10 @@ __global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const Pre
                        __int_as_float(radius_i), view_cos);
 }
 
-int launch_preprocess_fwd(const PreprocessArgs& a, cudaStream_t stream) {
-  if (a.P <= 0) return SOAR_OK;
+int launch_preprocess_fwd(const PreprocessArgs& a_in, cudaStream_t stream) {
+  if (a_in.P <= 0) return SOAR_OK;
+  PreprocessArgs a = a_in;
+  a.rot_vec = aligned16(a.rotations);
   {
     KernelScope ks(K_PREPROCESS, stream);
     const bool aligned = a.shs != nullptr && (reinterpret_cast<uintptr_t>(a.shs) & 15u) == 0;

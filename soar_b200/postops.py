@@ -30,14 +30,36 @@ def fov2focal(fov, pixels):
     return pixels / (2 * math.tan(fov / 2))
 
 
+# principal points already read back from the device: (data_ptr, version) -> (px, py). A camera's
+# prcppoint is a CUDA tensor in the reference (TS/renderer/gaussian_batch_renderer.py:59-82) that
+# never changes after the camera is built; reading it once per camera instead of once per render
+# keeps the render path free of blocking device->host copies.
+_PRCP_CACHE = {}
+
+
+def _prcp_host(pp):
+    if not torch.is_tensor(pp):
+        return np.asarray(pp, dtype=np.float32)
+    if not pp.is_cuda:
+        return pp.detach().float().numpy()
+    key = (pp.data_ptr(), pp._version, pp.device.index)
+    hit = _PRCP_CACHE.get(key)
+    # the weak reference guards against a different tensor re-using a freed address
+    if hit is not None and hit[0]() is pp:
+        return hit[1]
+    val = pp.detach().float().cpu().numpy()
+    if len(_PRCP_CACHE) > 4096:
+        _PRCP_CACHE.clear()
+    import weakref
+    _PRCP_CACHE[key] = (weakref.ref(pp), val)
+    return val
+
+
 def camera_constants(camera):
     """(cx, cy, kinv_x, kinv_y) exactly as depth2normal derives them (:375-382): the principal
     point in pixels as a float32 product, and the inverse of K = diag(fov2focal(FoVy, H),
     fov2focal(FoVx, W)) in float32 — the reference's own pairing of K00 with x."""
-    pp = camera.prcppoint
-    if torch.is_tensor(pp):
-        pp = pp.detach().float().cpu().numpy()
-    pp = np.asarray(pp, dtype=np.float32)
+    pp = np.asarray(_prcp_host(camera.prcppoint), dtype=np.float32)
     cx = np.float32(pp[0] * np.float32(camera.image_width))
     cy = np.float32(pp[1] * np.float32(camera.image_height))
     k00 = np.float32(fov2focal(camera.FoVy, camera.image_height))

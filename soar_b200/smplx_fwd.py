@@ -47,8 +47,7 @@ class SmplxPoser:
         m.v_template, m.shapedirs = self.v_template.data_ptr(), _capi.ptr(self.shapedirs)
         m.posedirs, m.J_regressor = self.posedirs.data_ptr(), self.J_regressor.data_ptr()
         m.parents, m.lbs_weights = self.parents.data_ptr(), self.lbs_weights.data_ptr()
-        self._ws = torch.empty(_lib.soar_smplx_workspace_bytes(self.V, self.J), dtype=torch.uint8,
-                               device=dev)
+        self._ws_bytes = _lib.soar_smplx_workspace_bytes(self.V, self.J)
 
     def __call__(self, betas, full_pose, transl=None, inv_mats=None, want_verts=True):
         """betas [NB] or [1,NB]; full_pose [J*3] / [1,J*3] / [J,3] axis-angle; transl [3] or None;
@@ -68,8 +67,11 @@ class SmplxPoser:
         bones = e(self.J, 4, 4) if inv is not None else None
         with torch.cuda.device(dev):
             stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+            # scratch per call, from the caching allocator (stream-ordered reuse): poses enqueued on
+            # different streams never share it
+            ws = torch.empty(self._ws_bytes, dtype=torch.uint8, device=dev)
             _capi.check(_lib.soar_smplx_forward(
                 ctypes.byref(self._model), _capi.ptr(betas), full_pose.data_ptr(), _capi.ptr(transl),
                 _capi.ptr(inv), _capi.ptr(verts), joints.data_ptr(), A.data_ptr(), _capi.ptr(bones),
-                self._ws.data_ptr(), self._ws.numel(), stream), "soar_smplx_forward")
+                ws.data_ptr(), ws.numel(), stream), "soar_smplx_forward")
         return verts, joints, A, bones

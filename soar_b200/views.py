@@ -65,6 +65,13 @@ def iter_view_pairs(pairs):
 # leaves straight into these slices (SoarRastGrads.accumulate_mask) and hands autograd `None` for
 # them: no per-view gradient tensors, no AccumulateGrad add kernels.
 _DIRECT = {}
+# the active FlatGrads.direct() context (None outside one)
+_ACTIVE = None
+
+
+def active_direct():
+    """The FlatGrads.direct() context a forward pass runs under (kept in its autograd ctx)."""
+    return _ACTIVE
 
 
 def direct_sink(t):
@@ -89,12 +96,14 @@ class FlatGrads:
         self.params = params
         sizes = [params[k].numel() for k in self.names]
         dev = params[self.names[0]].device
-        self.flat = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+        # every slice starts on a 16-byte boundary (the kernels move [P,4] and SH rows as float4:
+        # a slice at an odd float offset would force their scalar paths); the pad floats stay zero
         self.slices = {}
         off = 0
         for k, n in zip(self.names, sizes):
             self.slices[k] = (off, off + n)
-            off += n
+            off += (n + 3) // 4 * 4
+        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
         self.attach()
 
     def attach(self):
@@ -105,11 +114,15 @@ class FlatGrads:
     def zero_(self):
         self.flat.zero_()
 
-    def direct(self):
+    def direct(self, overwrite=False):
         """Context manager: inside it, rasterizer backward passes accumulate the gradients of
-        these parameters in place into the flat buffer (single stream; the buffer must have been
-        zeroed for the step). Gradients of anything else flow through autograd as usual."""
-        return _Direct(self)
+        these parameters in place into the flat buffer (single stream). Gradients of anything else
+        flow through autograd as usual. overwrite=False: the buffer must have been zeroed for the
+        step. overwrite=True: the FIRST backward inside the context stores (every element of every
+        registered parameter that takes part in it, zeros for culled Gaussians) and the following
+        ones add — no zero-fill, and the first view's read-modify-write traffic is gone. Parameters
+        that the first backward does not touch keep their old content: zero them yourself."""
+        return _Direct(self, overwrite)
 
     def grad(self, name: str) -> torch.Tensor:
         a, b = self.slices[name]
@@ -126,11 +139,25 @@ class FlatGrads:
 
 
 class _Direct:
-    def __init__(self, fg):
+    def __init__(self, fg, overwrite=False):
         self.fg = fg
         self.keys = []
+        self.overwrite = overwrite
+        self.stored = False
+
+    def first_store(self):
+        """True exactly once per `direct(overwrite=True)` context: the first rasterizer backward of
+        the views rendered under it STORES into the sinks (no zero-fill needed), later ones add."""
+        if not self.overwrite or self.stored:
+            return False
+        self.stored = True
+        return True
 
     def __enter__(self):
+        global _ACTIVE
+        if _ACTIVE is not None:
+            raise RuntimeError("FlatGrads.direct() contexts do not nest")
+        _ACTIVE = self
         for k in self.fg.names:
             p = self.fg.params[k]
             if p.is_cuda and p.is_contiguous():
@@ -139,6 +166,8 @@ class _Direct:
         return self.fg
 
     def __exit__(self, *exc):
+        global _ACTIVE
+        _ACTIVE = None
         for k in self.keys:
             _DIRECT.pop(k, None)
         return False

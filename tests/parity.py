@@ -1,0 +1,163 @@
+"""Comparison of the product rasterizer with the UNMODIFIED reference CUDA code (tests/refdgr.py ->
+oracle/_ref/libref_dgr.so) on one scene: the integer contract bit-exact, images <= 1e-4 max-abs,
+gradients <= 1e-3 relative — BASELINE.json north_star's bars — plus the per-element statistics the
+tensor-level figure hides.
+
+Every comparison appends one JSON line to gpurun_out/parity_report.jsonl (copied to profiles/ per
+round), so the error tables in DESIGN.md are the test run's own output."""
+import json
+import os
+
+import torch
+
+import refdgr
+from util import LEAVES, rel_err, settings_of
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REPORT = os.path.join(ROOT, "gpurun_out", "parity_report.jsonl")
+IMG_TOL = 1e-4
+GRAD_TOL = 1e-3
+SIGNIFICANT = 1e-3   # per-element statistics run over elements with |ref| > SIGNIFICANT * max|ref|
+
+
+def debug_tensors(s):
+    """Our private scratch decoded through soar_rast_debug_ptr / soar_rast_debug_sorted_keys (H7)."""
+    from diff_gaussian_rasterization import _C
+    from soar_b200 import _capi
+    lib = _capi.load()
+    e = torch.Tensor([])
+    opt = lambda k: s[k] if s.get(k) is not None else e
+    args = (s["bg"], s["means3D"], opt("colors_precomp"), s["opacities"], opt("scales"), opt("rotations"),
+            s["scale_modifier"], opt("cov3D_precomp"), s["viewmatrix"], s["projmatrix"], s["prcppoint"],
+            s["patch_bbox"], s["tanfovx"], s["tanfovy"], s["image_height"], s["image_width"], opt("shs"),
+            s["sh_degree"], s["campos"], s["prefiltered"], s["render_front"], s["sort_descending"],
+            False, s["config"])
+    R, color, normal, depth, opac, radii, geom, binning, img = _C.rasterize_gaussians(*args)
+    torch.cuda.synchronize()
+    P, H, W = s["means3D"].shape[0], s["image_height"], s["image_width"]
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    dev = s["means3D"].device
+
+    def grab(what, n, dtype):
+        p = lib.soar_rast_debug_ptr(what, P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr())
+        return refdgr._from_ptr(p, n, dtype, dev)
+
+    keys = torch.empty(R, dtype=torch.int64, device=dev)
+    _capi.check(lib.soar_rast_debug_sorted_keys(P, W, H, R, geom.data_ptr(), binning.data_ptr(),
+                                                keys.data_ptr() if R else None, None), "debug keys")
+    torch.cuda.synchronize()
+    return dict(R=R, keys=keys, point_list=grab(1, R, torch.int32),
+                ranges=grab(2, 2 * T, torch.int32).view(T, 2), n_contrib=grab(3, H * W, torch.int32),
+                radii=radii)
+
+
+def run_product(s, cot):
+    """Forward + backward through GaussianRasterizer with whichever of (scales, rotations) /
+    cov3D_precomp and shs / colors_precomp the scene holds. -> (outputs, grads keyed like refdgr's)."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    leaves = {}
+    for k in LEAVES + ("cov3D_precomp",):
+        v = s.get(k)
+        leaves[k] = None if v is None else v.detach().clone().requires_grad_(True)
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    rast = GaussianRasterizer(settings_of(s))
+    color, normal, depth, opac, radii = rast(
+        means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"], shs=leaves["shs"],
+        colors_precomp=leaves["colors_precomp"], scales=leaves["scales"], rotations=leaves["rotations"],
+        cov3D_precomp=leaves["cov3D_precomp"])
+    loss = ((color * cot["color"]).sum() + (normal * cot["normal"]).sum()
+            + (depth * cot["depth"]).sum() + (opac * cot["opac"]).sum())
+    loss.backward()
+    names = dict(means3D="means3D", opacities="opacity", scales="scales", rotations="rotations", shs="sh",
+                 colors_precomp="colors", cov3D_precomp="cov3D")
+    grads = {names[k]: v.grad for k, v in leaves.items() if v is not None}
+    grads["means2D"] = means2D.grad
+    out = dict(color=color.detach(), normal=normal.detach(), depth=depth.detach(), opac=opac.detach(), radii=radii)
+    return out, grads
+
+
+def element_stats(a, b):
+    """Per-element relative error of a against b over the elements of b that matter
+    (|b| > SIGNIFICANT * max|b|): median / 99th percentile / max, and the share of ALL elements
+    outside |a-b| <= 1e-3 |b| + 1e-5 max|b|."""
+    a, b = a.reshape(-1).double(), b.reshape(-1).double()
+    scale = b.abs().max().clamp_min(1e-30)
+    sig = b.abs() > SIGNIFICANT * scale
+    if sig.sum() == 0:
+        return dict(n=0, med=0.0, p99=0.0, max=0.0, outside=0.0)
+    rel = ((a - b).abs() / b.abs())[sig]
+    if rel.numel() > 4_000_000:   # torch.quantile's input limit; a fixed stride keeps it deterministic
+        relq = rel[:: rel.numel() // 4_000_000 + 1]
+    else:
+        relq = rel
+    q = torch.quantile(relq, torch.tensor([0.5, 0.99], dtype=torch.float64, device=rel.device))
+    outside = ((a - b).abs() > 1e-3 * b.abs() + 1e-5 * scale).double().mean()
+    return dict(n=int(sig.sum()), med=float(q[0]), p99=float(q[1]), max=float(rel.max()), outside=float(outside))
+
+
+def _log(rec):
+    try:
+        os.makedirs(os.path.dirname(REPORT), exist_ok=True)
+        with open(REPORT, "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+
+
+def compare_grads(name, ours, ref, ref_again, pairs, tag=None):
+    """Tensor-level bar (north_star): max|a-b| / max|b| <= max(1e-3, 10 x the reference's own
+    run-to-run figure). Per-element bar: the 99th-percentile relative error over significant
+    elements <= max(1e-3, 10 x the reference's own). Everything is printed and logged."""
+    rows, failures = {}, []
+    for k in pairs:
+        a, b, b2 = ours[k].reshape(-1), ref[k].reshape(-1), ref_again[k].reshape(-1)
+        assert torch.isfinite(a).all() or not torch.isfinite(b).all(), f"{name}: dL/d{k} has non-finite elements"
+        err, noise = rel_err(a, b), rel_err(b2, b)
+        st, st_noise = element_stats(a, b), element_stats(b2, b)
+        rows[k] = dict(err=err, noise=noise, elem=st, elem_noise=st_noise)
+        if err > max(GRAD_TOL, 10 * noise):
+            failures.append(f"dL/d{k}: tensor-relative {err:.3e} (reference self-noise {noise:.2e})")
+        if st["p99"] > max(GRAD_TOL, 10 * st_noise["p99"]):
+            failures.append(f"dL/d{k}: per-element p99 {st['p99']:.3e} (reference self-noise p99 {st_noise['p99']:.2e})")
+    line = " | ".join(f"{k}: {r['err']:.1e} (noise {r['noise']:.1e}; elem med {r['elem']['med']:.1e} "
+                      f"p99 {r['elem']['p99']:.1e} max {r['elem']['max']:.1e}, noise p99 {r['elem_noise']['p99']:.1e})"
+                      for k, r in rows.items())
+    print(f"[{name}] {line}")
+    _log(dict(case=name, tag=tag or os.environ.get("SOAR_BLEND_BWD_SCALAR", "packed"), grads=rows))
+    assert not failures, f"{name}: " + "; ".join(failures)
+    return rows
+
+
+def compare_with_reference(name, s, cot, private=True, grads=True):
+    """The whole contract for one scene. Returns (our outputs, reference outputs)."""
+    ref = refdgr.RefRasterizer()
+    r_out = ref.forward(s)
+    out, g = run_product(s, cot)
+    # ---- integer contract: bit-exact ---------------------------------------------------
+    assert torch.equal(out["radii"], r_out["radii"]), f"{name}: radii differ"
+    R = None
+    if private:
+        dbg = debug_tensors(s)
+        R = dbg["R"]
+        assert dbg["R"] == r_out["num_rendered"], (name, dbg["R"], r_out["num_rendered"])
+        assert torch.equal(dbg["keys"], ref.sorted_keys()), f"{name}: sorted tile|depth keys differ"
+        assert torch.equal(dbg["point_list"], ref.point_list()), f"{name}: sorted Gaussian ids differ"
+        assert torch.equal(dbg["ranges"], ref.ranges()), f"{name}: tile ranges differ"
+        assert torch.equal(dbg["n_contrib"], ref.n_contrib()), f"{name}: n_contrib differs"
+        del dbg
+    # ---- images -----------------------------------------------------------------------------
+    img_err = {}
+    for k in ("color", "normal", "depth", "opac"):
+        img_err[k] = (out[k] - r_out[k]).abs().max().item()
+        assert img_err[k] <= IMG_TOL, f"{name}: {k} max-abs {img_err[k]:.3e} > {IMG_TOL}"
+    _log(dict(case=name, R=R, visible=int((out["radii"] > 0).sum()), images=img_err))
+    # ---- gradients --------------------------------------------------------------------------
+    if grads:
+        r_g = ref.backward(cot)
+        r_g2 = ref.backward(cot)  # the reference's own atomic-order noise
+        pairs = ["means2D", "means3D", "opacity"]
+        pairs += ["scales", "rotations"] if s.get("scales") is not None else ["cov3D"]
+        pairs.append("sh" if s.get("shs") is not None else "colors")
+        compare_grads(name, g, r_g, r_g2, pairs)
+    ref.close()
+    return out, r_out

@@ -22,7 +22,7 @@ def _run(s, cot, scalar):
             os.environ.pop(k, None)
     try:
         out, g = T.run_ours(s, cot)
-        dbg = T._debug_tensors(s, out["radii"])
+        dbg = T.debug_tensors(s)
         torch.cuda.synchronize()
     finally:
         for k in ("SOAR_BLEND_FWD_SCALAR", "SOAR_BLEND_BWD_SCALAR"):
@@ -33,7 +33,7 @@ def _run(s, cot, scalar):
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_packed_kernels_match_scalar_twins(case):
-    name, P, W, H, deg, surfel, bg, desc, front = case
+    name, P, W, H, deg, surfel, bg, desc, front, _ = case
     s = T.to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=3, surfel=surfel, bg=bg,
                                     sort_descending=desc, render_front=front))
     cot = T.to_device(synthetic.cotangents(W, H, seed=3))

@@ -9,7 +9,7 @@ import torch
 import golden_util as G
 from oracle import rast_oracle
 from soar_b200 import synthetic
-from test_rasterizer_gpu import _debug_tensors
+from parity import debug_tensors
 from util import run_ours, to_device
 
 pytestmark = pytest.mark.gpu
@@ -24,7 +24,7 @@ def test_product_matches_golden(name):
     s = to_device(G.scene_of(d, as_torch=True))
     cot = to_device(G.cot_of(d, as_torch=True))
     out, g = run_ours(s, cot)
-    dbg = _debug_tensors(s, out["radii"])
+    dbg = debug_tensors(s)
     assert np.array_equal(out["radii"].cpu().numpy(), d["out_radii"])
     assert dbg["R"] == int(d["out_num_rendered"])
     assert np.array_equal(dbg["keys"].cpu().numpy().view(np.uint64), d["out_keys"])
@@ -82,7 +82,7 @@ def test_product_matches_cpu_oracle(kw):
     # on a rounding boundary of ceil(3 sigma); with equal radii everything downstream is compared
     assert mism <= 1e-4, f"radii mismatch rate {mism}"
     if mism == 0:
-        dbg = _debug_tensors(to_device(s_cpu), out["radii"])
+        dbg = debug_tensors(to_device(s_cpu))
         assert dbg["R"] == ref["num_rendered"]
         assert np.array_equal(dbg["point_list"].cpu().numpy().view(np.uint32), ref["point_list"])
         assert np.array_equal(dbg["ranges"].cpu().numpy().view(np.uint32), ref["ranges"])

@@ -1,0 +1,72 @@
+"""Where does the gradient deviation from the reference come from?
+
+Round 1 measured dL/dmeans2D 2e-4 (surfel_front) and 2.5e-5 (precomp_ragged) of the tensor's max
+against a reference run-to-run spread of 5e-7. The scalar twin of the blend backward can switch each
+arithmetic shortcut off separately (blend_bwd.cu, SOAR_BLEND_BWD_SCALAR = 1 + MODE bits):
+
+    bit 0  precise expf / IEEE division        instead of ex2.approx / rcp.approx
+    bit 1  the reference's per-channel recurrences and separate T_final terms
+    bit 2  dL/dmean2D summed per pixel with the reference's expression (not from moments at flush)
+
+This test runs the affected cases under every variant plus the packed product kernel, logs the
+error table (gpurun_out/parity_report.jsonl, summarised in DESIGN.md §6) and asserts what the
+attribution found: with all three bits set the scalar twin sits at the reference's own noise, and
+the product kernel stays inside the 1e-3 contract."""
+import os
+
+import pytest
+import torch
+
+import refdgr
+from parity import element_stats
+from soar_b200 import synthetic
+from util import rel_err, to_device
+import parity
+import test_rasterizer_gpu as T
+
+pytestmark = pytest.mark.gpu
+
+CASES = [c for c in T.CASES if c[0] in ("precomp_ragged", "surfel_front", "surfel_soar")]
+VARIANTS = [("packed", None), ("scalar", 1), ("scalar+precise", 2), ("scalar+perchannel", 3),
+            ("scalar+meandirect", 5), ("scalar+precise+perchannel", 4), ("scalar+all", 8)]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_gradient_deviation_attribution(case):
+    if not refdgr.available():
+        pytest.fail("oracle/_ref/libref_dgr.so missing")
+    name, P, W, H, deg, surfel, bg, desc, front, _ = case
+    s = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=3, surfel=surfel, bg=bg,
+                                  sort_descending=desc, render_front=front))
+    cot = to_device(synthetic.cotangents(W, H, seed=3))
+    ref = refdgr.RefRasterizer()
+    ref.forward(s)
+    r_g = ref.backward(cot)
+    r_g2 = ref.backward(cot)
+    keys = ["means2D", "means3D", "opacity", "scales", "rotations", "colors"]
+    table = {"reference-again": {k: (rel_err(r_g2[k].reshape(-1), r_g[k].reshape(-1)),
+                                     element_stats(r_g2[k], r_g[k])["p99"]) for k in keys}}
+    for label, env in VARIANTS:
+        if env is None:
+            os.environ.pop("SOAR_BLEND_BWD_SCALAR", None)
+        else:
+            os.environ["SOAR_BLEND_BWD_SCALAR"] = str(env)
+        try:
+            _, g = parity.run_product(s, cot)
+            torch.cuda.synchronize()
+        finally:
+            os.environ.pop("SOAR_BLEND_BWD_SCALAR", None)
+        table[label] = {k: (rel_err(g[k].reshape(-1), r_g[k].reshape(-1)), element_stats(g[k], r_g[k])["p99"])
+                        for k in keys}
+    ref.close()
+    print(f"\n[attribution {name}] tensor-relative error (per-element p99) vs the reference")
+    print(f"{'variant':28s} " + " ".join(f"{k:>21s}" for k in keys))
+    for label, row in table.items():
+        print(f"{label:28s} " + " ".join(f"{row[k][0]:9.2e} ({row[k][1]:8.2e})" for k in keys))
+    parity._log(dict(case=name, attribution={l: {k: list(v) for k, v in r.items()} for l, r in table.items()}))
+    noise = table["reference-again"]
+    for k in keys:
+        assert table["packed"][k][0] <= max(1e-3, 10 * noise[k][0]), f"packed: dL/d{k} {table['packed'][k][0]:.2e}"
+        # everything the reference does, done the reference's way, leaves only summation order
+        assert table["scalar+all"][k][0] <= max(2e-5, 20 * noise[k][0]), \
+            f"scalar+all: dL/d{k} {table['scalar+all'][k][0]:.2e} vs noise {noise[k][0]:.2e}"

@@ -165,3 +165,25 @@ def test_skin_weight_query_grid_is_bit_identical_to_brute_force(V, K):
     q.brute_force = True
     m_slow = q.mats(pts.cuda(), bones)
     assert ((m_fast == m_slow) | (m_fast.isnan() & m_slow.isnan())).all()
+
+
+@pytest.mark.parametrize("name", ("weights_full", "weights_dups", "weights_tiny"))
+def test_skin_weight_query_matches_reference_golden(name):
+    """Rows a18 / f1 against the reference's OWN lines: golden weights recorded by executing
+    SMPL_Guidance.query_weights_smpl (TS/utils/smpl.py:618-637) unchanged with an exact knn_points
+    stand-in (tests/golden/make_golden_weights.py) — on-vertex, near-surface, off-body, > 1 m away and
+    duplicated-vertex queries. Both the grid kernel and the brute-force kernel."""
+    import golden_util as G
+    from soar_b200.lbs import SkinWeightQuery
+    from test_lbs_oracle_golden import template_of
+    d = G.load(name)
+    verts, lw = template_of(d)
+    want = torch.from_numpy(d["weights"])
+    q = SkinWeightQuery(verts.cuda(), lw.cuda(), K=min(30, verts.shape[0]))
+    pts = torch.from_numpy(d["points"]).cuda()
+    for brute in (False, True):
+        q.brute_force = brute
+        got = q(pts).cpu()
+        err = (got - want).abs().max().item()
+        print(f"[{name}] {'brute' if brute else 'grid'}: max-abs {err:.2e}")
+        assert err <= 2e-6, f"{name} ({'brute' if brute else 'grid'}): {err:.2e}"

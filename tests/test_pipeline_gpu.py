@@ -56,42 +56,45 @@ def _loss(out, cot):
     return sum((out[k] * cot[k]).sum() for k in cot if out.get(k) is not None)
 
 
-def _scene_of(ar, cam, means, rots, scales, colors, bg, front):
+def _scene_of(ar, cam, means, rots, scales, colors, bg, front, descending=None):
+    """front = the render_front SETTING; descending defaults to the occupancy / legacy pairing."""
+    descending = (not front) if descending is None else descending
     return dict(means3D=means, rotations=rots, scales=scales, colors_precomp=colors, shs=None,
                 opacities=torch.ones((means.shape[0], 1), device="cuda"), bg=bg,
                 viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform,
                 campos=cam.camera_center, prcppoint=cam.prcppoint, patch_bbox=cam.full_patch(),
                 tanfovx=math.tan(cam.FoVx * 0.5), tanfovy=math.tan(cam.FoVy * 0.5),
                 image_height=cam.image_height, image_width=cam.image_width, scale_modifier=1.0,
-                sh_degree=0, prefiltered=False, render_front=front, sort_descending=not front,
+                sh_degree=0, prefiltered=False, render_front=front, sort_descending=descending,
                 debug=False, config=ar.config)
 
 
-def _ours(ar, g, pts, scale2d, bones, cam, cot, sds, weights=None):
+def _ours(ar, g, pts, scale2d, bones, cam, cot, sds, weights=None, render_front=True):
     leaves = dict(points=pts.clone().requires_grad_(True), rot=g["rot"].cuda().requires_grad_(True),
                   colors=g["colors"].cuda().requires_grad_(True),
                   scale2d=scale2d.clone().requires_grad_(True))
     w = ar.weights(leaves["points"]) if weights is None else weights
     bg = torch.zeros(3, device="cuda")
     out = ar.render(leaves["points"], leaves["rot"], w, bones, leaves["colors"], leaves["scale2d"],
-                    g["occ"].cuda(), cam, bg, sds_view=sds)
+                    g["occ"].cuda(), cam, bg, sds_view=sds, render_front=render_front)
     _loss(out, cot).backward()
     return out, {k: v.grad for k, v in leaves.items()}, w
 
 
-def _mute_degenerate(ar, g, pts, scale2d, bones, cam, cot, sds):
+def _mute_degenerate(ar, g, pts, scale2d, bones, cam, cot, sds, render_front=True):
     """Zero the pred_normal cotangent on degenerate depth2normal stencils: there the reference's
     F.normalize backward makes 1e12-scale terms whose cancellation is order-dependent noise
     (oracle/postops_oracle.py header), which would swamp a 1e-3 comparison of the chain."""
     with torch.no_grad():
         o = ar.render(pts, g["rot"].cuda(), ar.weights(pts), bones, g["colors"].cuda(), scale2d,
-                      g["occ"].cuda(), cam, torch.zeros(3, device="cuda"), sds_view=sds, render_occ=False)
+                      g["occ"].cuda(), cam, torch.zeros(3, device="cuda"), sds_view=sds, render_occ=False,
+                      render_front=render_front)
         deg = (o["mask"][0] > 1e-5) & ((o["pred_normal"] * 2 - 1).norm(dim=0) < 0.5)
         cot["pred_normal"][:, deg] = 0
     return deg
 
 
-def _checker_chain(ar, g, pts, scale2d, bones, cam, cot, sds):
+def _checker_chain(ar, g, pts, scale2d, bones, cam, cot, sds, render_front=True):
     """The same step from the checkers: torch skinning oracle (CPU, autograd) -> reference CUDA
     rasterizer fwd/bwd -> post-op oracle (torch on the device, autograd)."""
     from oracle import lbs_oracle, postops_oracle
@@ -111,7 +114,10 @@ def _checker_chain(ar, g, pts, scale2d, bones, cam, cot, sds):
                                    ar.weights(pts), bones, swizzle=sds)
     assert (op.cpu() - sp.detach()).abs().max().item() <= 5e-6, "skinned points differ from the oracle"
     assert (oq.cpu() - sq.detach()).abs().max().item() <= 5e-5, "skinned quaternions differ from the oracle"
-    s = _scene_of(ar, cam, op.contiguous(), oq.contiguous(), scales, g["colors"].cuda(), bg, front=False)
+    # the main pass: render_front SETTING False, sorted descending iff the render_front ARGUMENT is
+    # False (TS/renderer/diff_gaussian_rasterizer.py:186-187)
+    s = _scene_of(ar, cam, op.contiguous(), oq.contiguous(), scales, g["colors"].cuda(), bg, front=False,
+                  descending=not render_front)
     ref = refdgr.RefRasterizer()
     ro = ref.forward(s)
     img = {k: ro[k].clone().requires_grad_(True) for k in ("color", "normal", "depth", "opac")}
@@ -134,16 +140,17 @@ def _checker_chain(ar, g, pts, scale2d, bones, cam, cot, sds):
     return outs, grads
 
 
+@pytest.mark.parametrize("render_front", [True, False])
 @pytest.mark.parametrize("sds", [False, True])
-def test_full_chain_matches_checker_chain(sds):
+def test_full_chain_matches_checker_chain(sds, render_front):
     if not refdgr.available():
         pytest.fail("oracle/_ref/libref_dgr.so missing: run oracle/build_ref.sh where /root/reference is mounted")
     W, H, N = 320, 256, 20_000
     ar, g, pts, scale2d, bones, cams = _avatar(N, W, H, seed=3, V=2000)
     cot = _cots(W, H, seed=11)
-    _mute_degenerate(ar, g, pts, scale2d, bones, cams[0], cot, sds)
-    out, grads, w = _ours(ar, g, pts, scale2d, bones, cams[0], cot, sds)
-    ro, rg = _checker_chain(ar, g, pts, scale2d, bones, cams[0], cot, sds)
+    _mute_degenerate(ar, g, pts, scale2d, bones, cams[0], cot, sds, render_front)
+    out, grads, w = _ours(ar, g, pts, scale2d, bones, cams[0], cot, sds, render_front=render_front)
+    ro, rg = _checker_chain(ar, g, pts, scale2d, bones, cams[0], cot, sds, render_front)
     assert (w.cpu() - ro["weights"]).abs().max().item() <= 2e-5
     assert torch.equal(out["radii"], ro["radii"]), "radii differ from the reference"
     assert (out["radii"] > 0).float().mean().item() > 0.2   # random surfel orientations: about half face away
@@ -174,29 +181,40 @@ def test_c5_dance_step_2m_gaussians_1080p():
         assert torch.isfinite(v).all(), f"dL/d{k} not finite"
     assert (grads["colors"][~vis] == 0).all() and (grads["scale2d"][~vis] == 0).all()
     assert out["mask"].min().item() >= 0 and out["mask"].max().item() <= 1
-    # the rasterizer stage vs the reference on the skinned Gaussians
-    if refdgr.available():
-        from soar_b200.lbs import skin_gaussians
-        with torch.no_grad():
-            sp, sq, _ = skin_gaussians(pts, torch.nn.functional.normalize(g["rot"].cuda(), dim=-1), w, bones)
-        scales = scale2d.repeat(1, 3); scales[:, 2] = -1e10
-        s = _scene_of(ar, cams[0], sp, sq, scales, g["colors"].cuda(), torch.zeros(3, device="cuda"), False)
-        ref = refdgr.RefRasterizer()
-        ro = ref.forward(s)
-        assert torch.equal(out["radii"], ro["radii"])
-        for ours, theirs in (("render", "color"), ("depth", "depth"), ("mask", "opac")):
-            err = (out[ours].detach() - ro[theirs]).abs().max().item()
-            assert err <= IMG_TOL, f"{ours}: {err:.2e}"
-        ref.close()
+    # the rasterizer stage vs the reference on the skinned Gaussians: the whole contract (integer
+    # state bit-exact, the four images, every gradient tensor with per-element statistics)
+    if not refdgr.available():
+        pytest.fail("oracle/_ref/libref_dgr.so missing: run oracle/build_ref.sh where /root/reference is mounted")
+    from parity import compare_with_reference
+    from soar_b200.lbs import skin_gaussians
+    with torch.no_grad():
+        sp, sq, _ = skin_gaussians(pts, torch.nn.functional.normalize(g["rot"].cuda(), dim=-1), w, bones)
+    scales = scale2d.repeat(1, 3); scales[:, 2] = -1e10
+    s = _scene_of(ar, cams[0], sp, sq, scales, g["colors"].cuda(), torch.zeros(3, device="cuda"), False,
+                  descending=False)
+    cot4 = {k: v.cuda() for k, v in synthetic.cotangents(W, H, seed=5).items()}
+    o, ro = compare_with_reference("c5_raster_2M_1080p", s, cot4)
+    assert torch.equal(out["radii"], ro["radii"])
+    # ... and the chain's own images are that rasterizer pass
+    for ours, theirs in (("render", "color"), ("depth", "depth"), ("mask", "opac")):
+        err = (out[ours].detach() - ro[theirs]).abs().max().item()
+        assert err <= IMG_TOL, f"{ours}: {err:.2e}"
+    flipped = ro["normal"].clone(); flipped[1:] *= -1        # the post block: (n * (1,-1,-1) + 1) / 2
+    err = (out["normal"].detach() - (flipped + 1) / 2).abs().max().item()
+    assert err <= IMG_TOL, f"normal: {err:.2e}"
+    del o, ro
     # KNN on the skinned cloud (the densify re-initialisation reads it): positive, finite
     d2 = distCUDA2(pts)
     assert torch.isfinite(d2).all() and (d2 >= 0).all() and d2.shape == (N,)
 
 
-def test_c4_sds_step_32_views_matches_per_view_sum():
-    """BASELINE config 4: 32 SDS views at 512² of one pose. iter_views + in-place accumulation
-    (what a rank does with its shard of the views) must equal the sum of 32 independent
-    fwd+bwd passes, and shard_views must split the 32 views evenly over 2/4/8 ranks."""
+def test_c4_sds_step_32_views_matches_reference():
+    """BASELINE config 4: 32 SDS views at 512² of one pose. The multi-view path (iter_views + in-place
+    accumulation — what a rank does with its shard of the views) against the UNMODIFIED reference:
+    every view's four images, and the gradient summed over the 32 views (reference passes summed in
+    float64). shard_views must split the 32 views evenly over 2/4/8 ranks."""
+    if not refdgr.available():
+        pytest.fail("oracle/_ref/libref_dgr.so missing: run oracle/build_ref.sh where /root/reference is mounted")
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     from soar_b200.lbs import skin_gaussians
     from soar_b200.views import FlatGrads, iter_views, shard_views
@@ -212,13 +230,14 @@ def test_c4_sds_step_32_views_matches_per_view_sum():
     ones = torch.ones((N, 1), device="cuda")
     bg = torch.zeros(3, device="cuda")
     cot = _cots(W, H, seed=2)
+    patch = cams[0].full_patch()
 
     def rast(cam):
         return GaussianRasterizer(GaussianRasterizationSettings(
             image_height=H, image_width=W, tanfovx=math.tan(cam.FoVx / 2), tanfovy=math.tan(cam.FoVy / 2),
             bg=bg, scale_modifier=1.0, viewmatrix=cam.world_view_transform, projmatrix=cam.full_proj_transform,
-            patch_bbox=cam.full_patch(), prcppoint=cam.prcppoint, sh_degree=0, campos=cam.camera_center,
-            prefiltered=False, render_front=False, sort_descending=True, debug=False, config=ar.config))
+            patch_bbox=patch, prcppoint=cam.prcppoint, sh_degree=0, campos=cam.camera_center,
+            prefiltered=False, render_front=False, sort_descending=False, debug=False, config=ar.config))
 
     def kw():
         return dict(means3D=params["means3D"], means2D=torch.zeros_like(sp, requires_grad=True),
@@ -229,23 +248,37 @@ def test_c4_sds_step_32_views_matches_per_view_sum():
         return (o[0] * cot["render"]).sum() + (o[1] * cot["normal"]).sum() + (o[2] * cot["depth"]).sum() \
             + (o[3] * cot["mask"]).sum()
 
-    # independent passes, summed in float64
-    want = {k: torch.zeros_like(v, dtype=torch.float64) for k, v in params.items()}
-    for cam in cams:
-        for p in params.values():
-            p.grad = None
-        loss(rast(cam)(**kw())).backward()
-        for k, p in params.items():
-            want[k] += p.grad.double()
-    # the multi-view step
+    # the multi-view step; no zero-fill: the first backward of the step stores
     flat = FlatGrads(params)
-    flat.zero_()
-    with flat.direct():
+    flat.flat.fill_(float("nan"))   # whatever the buffer held must not survive the first view
+    images = []
+    with flat.direct(overwrite=True):
         for o in iter_views([rast(c) for c in cams], [kw() for _ in cams]):
+            images.append([t.detach().clone() for t in o[:4]])
             loss(o).backward()
+    # the reference, view by view
+    ref = refdgr.RefRasterizer()
+    rcot = dict(color=cot["render"], normal=cot["normal"], depth=cot["depth"], opac=cot["mask"])
+    want = {k: torch.zeros_like(v, dtype=torch.float64) for k, v in params.items()}
+    names = dict(means3D="means3D", colors_precomp="colors", scales="scales", rotations="rotations")
+    worst = 0.0
+    for v, cam in enumerate(cams):
+        s = _scene_of(ar, cam, sp, sq, scales, g["colors"].cuda(), bg, False, descending=False)
+        ro = ref.forward(s)
+        for img, k in zip(images[v], ("color", "normal", "depth", "opac")):
+            err = (img - ro[k]).abs().max().item()
+            worst = max(worst, err)
+            assert err <= IMG_TOL, f"view {v}: {k} max-abs {err:.2e}"
+        rg = ref.backward(rcot)
+        for k in params:
+            want[k] += rg[names[k]].double().view_as(want[k])
+    ref.close()
+    report = []
     for k in params:
         e = rel_err(flat.grad(k).double().view_as(want[k]), want[k])
+        report.append(f"{k}: {e:.2e}")
         assert e <= GRAD_TOL, f"{k}: {e:.2e}"
+    print(f"[c4_32_views] worst image max-abs {worst:.2e}; summed gradients vs reference: " + " | ".join(report))
     for world in (2, 4, 8):
         shards = [shard_views(V, r, world) for r in range(world)]
         assert sorted(sum(shards, [])) == list(range(V)) and {len(s) for s in shards} == {V // world}

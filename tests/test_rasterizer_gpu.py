@@ -9,13 +9,11 @@ import pytest
 import torch
 
 import refdgr
+from parity import IMG_TOL, compare_with_reference, debug_tensors
 from soar_b200 import synthetic
-from util import rel_err, run_ours, settings_of, to_device
+from util import run_ours, settings_of, to_device
 
 pytestmark = pytest.mark.gpu
-
-IMG_TOL = 1e-4
-GRAD_TOL = 1e-3
 
 
 def _need_ref():
@@ -23,89 +21,79 @@ def _need_ref():
         pytest.fail("oracle/_ref/libref_dgr.so missing: run oracle/build_ref.sh where /root/reference is mounted")
 
 
-def _debug_tensors(s, out_radii):
-    """Decode our private scratch buffers through soar_rast_debug_ptr (H7)."""
-    from diff_gaussian_rasterization import _C
-    from soar_b200 import _capi
-    lib = _capi.load()
-    args = (s["bg"], s["means3D"], s.get("colors_precomp") if s.get("colors_precomp") is not None else torch.Tensor([]),
-            s["opacities"], s["scales"], s["rotations"], s["scale_modifier"], torch.Tensor([]),
-            s["viewmatrix"], s["projmatrix"], s["prcppoint"], s["patch_bbox"], s["tanfovx"], s["tanfovy"],
-            s["image_height"], s["image_width"], s["shs"] if s.get("shs") is not None else torch.Tensor([]),
-            s["sh_degree"], s["campos"], s["prefiltered"], s["render_front"], s["sort_descending"],
-            False, s["config"])
-    R, color, normal, depth, opac, radii, geom, binning, img = _C.rasterize_gaussians(*args)
-    torch.cuda.synchronize()
-    P, H, W = s["means3D"].shape[0], s["image_height"], s["image_width"]
-    T = ((W + 15) // 16) * ((H + 15) // 16)
+def _cov3d_from_scale_rot(scales, rotations):
+    """Sigma = R diag(s^2) R^T as the 6 upper-triangular entries — any symmetric PSD 6-vector is a
+    valid cov3D_precomp; this one makes the scene look like its scale/rotation twin."""
+    q = torch.nn.functional.normalize(rotations, dim=1)
+    r, x, y, z = q.unbind(1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], 1).view(-1, 3, 3)
+    S = R @ torch.diag_embed(scales * scales) @ R.transpose(1, 2)
+    return torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).contiguous()
 
-    def grab(what, n, dtype):
-        p = lib.soar_rast_debug_ptr(what, P, W, H, R, geom.data_ptr(), binning.data_ptr(), img.data_ptr())
-        return refdgr._from_ptr(p, n, dtype, s["means3D"].device)
 
-    keys = torch.empty(R, dtype=torch.int64, device=s["means3D"].device)
-    _capi.check(lib.soar_rast_debug_sorted_keys(P, W, H, R, geom.data_ptr(), binning.data_ptr(),
-                                                keys.data_ptr() if R else None, None), "debug keys")
-    torch.cuda.synchronize()
-    return dict(R=R, keys=keys, point_list=grab(1, R, torch.int32),
-                ranges=grab(2, 2 * T, torch.int32).view(T, 2), n_contrib=grab(3, H * W, torch.int32),
-                radii=radii)
+def _variant(s, kind):
+    """Scene variations the real loop produces."""
+    H, W = s["image_height"], s["image_width"]
+    dev = s["means3D"].device
+    if kind == "patch":
+        # camera.random_patch(h_size, w_size): (h0, w0, h1, w1) of a sub-window
+        # (TS/geometry/gaussian_base.py:220-229; renderer :182)
+        s["patch_bbox"] = torch.tensor([37.0, 91.0, 37.0 + 0.55 * H // 1, 91.0 + 0.6 * W // 1], device=dev)
+    elif kind == "prcp":
+        # gt views carry the principal point (cx / W, cy / H) of the video's intrinsics
+        # (TS/renderer/gaussian_batch_renderer.py:59-82)
+        s["prcppoint"] = torch.tensor([0.4375, 0.5703], device=dev)
+    elif kind == "scale_mod":
+        s["scale_modifier"] = 0.7
+    elif kind == "scale_mod_big":
+        s["scale_modifier"] = 1.6
+    elif kind == "cov3d":
+        s["cov3D_precomp"] = _cov3d_from_scale_rot(s["scales"], s["rotations"])
+        s["scales"] = s["rotations"] = None
+    elif kind is not None:
+        raise KeyError(kind)
+    return s
 
 
 CASES = [
-    # name, P, W, H, sh_degree, surfel, bg, descending, render_front
-    ("c2_sh0_512", 100_000, 512, 512, 0, False, (0.0, 0.0, 0.0), False, False),
-    ("sh3_640x360", 60_000, 640, 360, 3, False, (1.0, 1.0, 1.0), False, False),
-    ("precomp_ragged", 30_000, 500, 333, None, False, (0.2, 0.4, 0.6), False, False),
-    ("surfel_soar", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False),
-    ("surfel_front", 50_000, 512, 512, None, True, (1.0, 1.0, 1.0), False, True),
-    ("tiny", 7, 64, 48, 1, False, (0.0, 0.0, 0.0), False, False),
+    # name, P, W, H, sh_degree, surfel, bg, descending, render_front, variant
+    ("c2_sh0_512", 100_000, 512, 512, 0, False, (0.0, 0.0, 0.0), False, False, None),
+    ("sh3_640x360", 60_000, 640, 360, 3, False, (1.0, 1.0, 1.0), False, False, None),
+    ("precomp_ragged", 30_000, 500, 333, None, False, (0.2, 0.4, 0.6), False, False, None),
+    ("surfel_soar", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False, None),
+    ("surfel_front", 50_000, 512, 512, None, True, (1.0, 1.0, 1.0), False, True, None),
+    ("tiny", 7, 64, 48, 1, False, (0.0, 0.0, 0.0), False, False, None),
+    # what the real loop adds (renderer :182-183, gaussian_batch_renderer.py:59-82)
+    ("patch_bbox_sh1", 60_000, 640, 360, 1, False, (0.0, 0.0, 0.0), False, False, "patch"),
+    ("patch_bbox_surfel", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False, "patch"),
+    ("prcppoint_sh2", 60_000, 640, 360, 2, False, (0.1, 0.1, 0.1), False, False, "prcp"),
+    ("prcppoint_surfel", 50_000, 500, 333, None, True, (0.0, 0.0, 0.0), False, False, "prcp"),
+    ("scale_modifier_0.7", 60_000, 512, 512, 0, False, (0.0, 0.0, 0.0), False, False, "scale_mod"),
+    ("scale_modifier_surfel_q2", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False, "scale_mod_big"),
+    ("cov3D_precomp", 40_000, 512, 384, 1, False, (0.3, 0.3, 0.3), False, False, "cov3d"),
+    # BASELINE config 3, the configuration every throughput figure is quoted on
+    ("c3_sh3_1024_500k", 500_000, 1024, 1024, 3, False, (0.0, 0.0, 0.0), False, False, None),
 ]
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
 def test_forward_backward_matches_reference(case):
     _need_ref()
-    name, P, W, H, deg, surfel, bg, desc, front = case
-    s = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=3, surfel=surfel, bg=bg,
+    name, P, W, H, deg, surfel, bg, desc, front, variant = case
+    seed = 0 if name.startswith("c3_") else 3   # c3: the bench's own scene
+    s = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=seed, surfel=surfel, bg=bg,
                                   sort_descending=desc, render_front=front))
-    cot = to_device(synthetic.cotangents(W, H, seed=3))
-
-    ref = refdgr.RefRasterizer()
-    r_out = ref.forward(s)
-    r_g = ref.backward(cot)
-    r_g2 = ref.backward(cot)  # the reference's own atomic-order noise
-
-    out, g = run_ours(s, cot)
-    dbg = _debug_tensors(s, out["radii"])
-
-    # ---- integer contract: bit-exact ------------------------------------------------
-    assert torch.equal(out["radii"], r_out["radii"]), "radii differ"
-    assert dbg["R"] == r_out["num_rendered"], (dbg["R"], r_out["num_rendered"])
-    assert torch.equal(dbg["keys"], ref.sorted_keys()), "sorted tile|depth keys differ"
-    assert torch.equal(dbg["point_list"], ref.point_list()), "sorted Gaussian ids differ"
-    assert torch.equal(dbg["ranges"], ref.ranges()), "tile ranges differ"
-    assert torch.equal(dbg["n_contrib"], ref.n_contrib()), "n_contrib differs"
-
-    # ---- images -------------------------------------------------------------------------
-    for k in ("color", "normal", "depth", "opac"):
-        err = (out[k] - r_out[k]).abs().max().item()
-        assert err <= IMG_TOL, f"{name}: {k} max-abs {err:.3e} > {IMG_TOL}"
-
-    # ---- gradients ------------------------------------------------------------------------
-    pairs = [("means2D", "means2D"), ("means3D", "means3D"), ("opacity", "opacity"),
-             ("scales", "scales"), ("rotations", "rotations")]
-    pairs.append(("sh", "sh") if deg is not None else ("colors", "colors"))
-    report = []
-    for ours_k, ref_k in pairs:
-        a, b = g[ours_k].reshape(-1), r_g[ref_k].reshape(-1)
-        noise = rel_err(r_g2[ref_k].reshape(-1), b)
-        err = rel_err(a, b)
-        report.append(f"{ours_k}: err {err:.2e} (ref self-noise {noise:.2e})")
-        assert torch.isfinite(a).all() or not torch.isfinite(b).all(), f"{ours_k}: non-finite gradient"
-        assert err <= max(GRAD_TOL, 10 * noise), f"{name}: grad {ours_k} rel err {err:.3e}; " + "; ".join(report)
-    print(f"[{name}] R={dbg['R']} " + " | ".join(report))
-    ref.close()
+    s = _variant(s, variant)
+    cot = to_device(synthetic.cotangents(W, H, seed=seed))
+    out, r_out = compare_with_reference(name, s, cot)
+    if P > 1000:
+        assert (out["radii"] > 0).float().mean().item() > 0.05, "degenerate case: almost nothing visible"
+    if variant == "patch":   # the sub-window really culls
+        full = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=seed, surfel=surfel, bg=bg,
+                                         sort_descending=desc, render_front=front))
+        assert (out["radii"] > 0).sum().item() < (run_ours(full)[0]["radii"] > 0).sum().item()
 
 
 def test_empty_input():
@@ -143,23 +131,22 @@ def test_argument_validation_like_reference():
     assert rast.markVisible(s["means3D"]).sum().item() == 0  # Q11: all-false
 
 
-def test_full_size_properties_c3():
-    """BASELINE config 3 (1024^2, 500k, SH3): size-independent properties — sorted keys are
-    non-decreasing, ranges partition the list, opacity in [0,1], gradients finite, and a
-    second run reproduces the integer state exactly."""
+def test_integer_state_is_reproducible_c3():
+    """BASELINE config 3 twice: the sorted list and every integer output must repeat exactly (the
+    decoupled look-back scans and the onesweep sort are order-free by construction), keys are
+    non-decreasing, ranges partition the list, culled Gaussians get exactly zero gradient. The
+    comparison of c3 with the reference is the c3_sh3_1024_500k case above."""
     s = to_device(synthetic.scene(500_000, 1024, 1024, sh_degree=3, seed=0))
     cot = to_device(synthetic.cotangents(1024, 1024, seed=0))
     out, g = run_ours(s, cot)
-    d1 = _debug_tensors(s, out["radii"])
-    d2 = _debug_tensors(s, out["radii"])
+    d1 = debug_tensors(s)
+    d2 = debug_tensors(s)
     assert d1["R"] == d2["R"] and torch.equal(d1["keys"], d2["keys"]) and torch.equal(d1["point_list"], d2["point_list"])
+    assert torch.equal(d1["n_contrib"], d2["n_contrib"]) and torch.equal(d1["ranges"], d2["ranges"])
     keys = d1["keys"]
     assert (keys[1:] >= keys[:-1]).all(), "keys not sorted"
     rng = d1["ranges"].long()
-    covered = (rng[:, 1] - rng[:, 0]).sum().item()
-    assert covered == d1["R"], "ranges do not partition the pair list"
+    assert (rng[:, 1] - rng[:, 0]).sum().item() == d1["R"], "ranges do not partition the pair list"
     assert out["opac"].min().item() >= 0.0 and out["opac"].max().item() <= 1.0
-    for k, v in g.items():
-        assert torch.isfinite(v).all(), f"grad {k} not finite"
     vis = out["radii"] > 0
     assert (g["means3D"][~vis] == 0).all(), "culled Gaussians must get zero gradient"

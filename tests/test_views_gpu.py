@@ -102,3 +102,95 @@ def test_direct_accumulation_ignores_unregistered_and_derived_tensors():
     _loss(GaussianRasterizer(settings_of(s))(**_kwargs(plain)), cot).backward()
     for k in KEYS:
         assert rel_err(flat.grad(k), plain[k].grad) <= 1e-3, k
+
+
+def test_begin_rejects_changed_or_modified_arguments():
+    """forward() after begin() must see the SAME arguments: a different scales / opacities / SH
+    tensor, an in-place update in between, or swapped settings would otherwise render the geometry
+    begin() preprocessed."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scenes, _ = _views(5_000, 128, 96, 2, sh_degree=1)
+    s = scenes[0]
+    params = {k: s[k].clone() for k in KEYS}
+    for key in ("scales", "rotations", "opacities", "shs"):
+        r = GaussianRasterizer(settings_of(s))
+        kw = _kwargs(params)
+        r.begin(**kw)
+        kw2 = dict(kw)
+        kw2[key] = params[key].clone()
+        with pytest.raises(RuntimeError):
+            r(**kw2)
+    r = GaussianRasterizer(settings_of(s))
+    kw = _kwargs(params)
+    r.begin(**kw)
+    params["scales"].mul_(1.5)   # same storage, new content
+    with pytest.raises(RuntimeError):
+        r(**kw)
+    r = GaussianRasterizer(settings_of(s))
+    kw = _kwargs(params)
+    r.begin(**kw)
+    r.raster_settings = settings_of(scenes[1])
+    with pytest.raises(RuntimeError):
+        r(**kw)
+
+
+@pytest.mark.parametrize("P", [10_001, 10_002, 10_003])
+def test_direct_accumulation_with_P_not_a_multiple_of_4(P):
+    """with P % 4 != 0 an unpadded flat buffer put the rotations sink at an odd
+    float offset and the 16-byte red.global.add faulted. FlatGrads now pads every slice to 16 bytes;
+    overwrite=True covers the store path."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    scenes, cot = _views(P, 160, 128, 2, sh_degree=3)
+    base = {k: scenes[0][k] for k in KEYS}
+    ref = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    for s in scenes:
+        _loss(GaussianRasterizer(settings_of(s))(**_kwargs(ref)), cot).backward()
+    got = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    flat = FlatGrads(got)
+    for k in KEYS:
+        assert flat.grad(k).data_ptr() % 16 == 0, f"slice {k} is not 16-byte aligned"
+    flat.flat.fill_(7.0)
+    with flat.direct(overwrite=True):
+        for s in scenes:
+            _loss(GaussianRasterizer(settings_of(s))(**_kwargs(got)), cot).backward()
+    torch.cuda.synchronize()
+    for k in KEYS:
+        assert rel_err(flat.grad(k), ref[k].grad) <= 1e-3, k
+
+
+def test_misaligned_rotation_pointers_take_the_scalar_path():
+    """Caller-owned [P,4] tensors at an odd float offset (a slice of somebody else's flat buffer): the
+    launchers must notice and fall back to scalar loads / stores / reductions instead of faulting."""
+    from diff_gaussian_rasterization import _C
+    P = 9_001
+    s = to_device(synthetic.scene(P, 160, 128, sh_degree=1, seed=5))
+    cot = to_device(synthetic.cotangents(160, 128, seed=5))
+    e = torch.Tensor([])
+
+    def run(rot, sink):
+        out = _C.rasterize_gaussians(s["bg"], s["means3D"], e, s["opacities"], s["scales"], rot, 1.0, e,
+                                     s["viewmatrix"], s["projmatrix"], s["prcppoint"], s["patch_bbox"],
+                                     s["tanfovx"], s["tanfovy"], 128, 160, s["shs"], 1, s["campos"], False,
+                                     False, False, False, s["config"])
+        R, color, normal, depth, opac, radii, geom, binning, img = out
+        g = _C.rasterize_gaussians_backward(
+            s["bg"], s["means3D"], radii, e, s["scales"], rot, 1.0, e, s["viewmatrix"], s["projmatrix"],
+            s["prcppoint"], s["patch_bbox"], s["tanfovx"], s["tanfovy"], cot["color"], cot["normal"],
+            cot["depth"], cot["opac"], s["shs"], 1, s["campos"], geom, R, binning, img, False, s["config"],
+            {"rotations": sink} if sink is not None else None)
+        torch.cuda.synchronize()
+        return color, g[7]
+
+    color0, grot0 = run(s["rotations"], None)
+    store = torch.zeros(4 * P + 1, device="cuda")
+    store[1:] = s["rotations"].reshape(-1)
+    rot_odd = store[1:].view(P, 4)
+    sink_store = torch.zeros(4 * P + 3, device="cuda")
+    sink = sink_store[3:].view(P, 4)
+    assert rot_odd.data_ptr() % 16 != 0 and sink.data_ptr() % 16 != 0
+    color1, grot1 = run(rot_odd, sink)
+    assert torch.equal(color0, color1)
+    assert grot1.data_ptr() == sink.data_ptr()
+    assert rel_err(sink, grot0) <= 1e-3
+    color2, _ = run(rot_odd, sink)          # accumulates a second time
+    assert rel_err(sink, 2 * grot0) <= 1e-3
