@@ -220,6 +220,17 @@ int soar_lbs_query_weights_grid(const float* points, int32_t N, const void* grid
                                 const float* lbs_weights, int32_t J, int32_t K, const float* bones,
                                 float* out_weights, float* out_mats, soar_stream_t stream);
 
+/* The same query, batched for large N (exact, bit-identical results): the queries are sorted by grid
+ * cell with the library's own radix sort and a warp walks the search cube of a cell once for all its
+ * queries (lbs_query.cu). `workspace` holds the sort's ping-pong buffers,
+ * soar_lbs_query_cells_workspace_bytes(N) bytes. K != 30, V > 13000, small N or a NULL workspace
+ * take soar_lbs_query_weights_grid's per-point walk. */
+size_t soar_lbs_query_cells_workspace_bytes(int32_t N);
+int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* grid, int32_t V,
+                                 const float* lbs_weights, int32_t J, int32_t K, const float* bones,
+                                 float* out_weights, float* out_mats, void* workspace,
+                                 size_t workspace_bytes, soar_stream_t stream);
+
 /* ---- SMPL-X body-model forward for one pose (replaces smplx.lbs.lbs(),
  *      TS/utils/smplx/lbs.py:147-246, plus the transl fold of SMPLX.forward,
  *      TS/utils/smplx/body_models.py:1380-1383, and the cano->live bones of

@@ -186,6 +186,12 @@ SIGNATURES = {
         [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
          c_void_p, c_void_p],
     ),
+    "soar_lbs_query_cells_workspace_bytes": (c_size_t, [c_int32]),
+    "soar_lbs_query_weights_cells": (
+        c_int32,
+        [c_void_p, c_int32, c_void_p, c_int32, c_void_p, c_int32, c_int32, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
     "soar_smplx_workspace_bytes": (c_size_t, [c_int32, c_int32]),
     "soar_smplx_forward": (
         c_int32,

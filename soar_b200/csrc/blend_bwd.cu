@@ -34,6 +34,16 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// The replay must take the forward's (= the reference's) per-pixel decision `alpha < 1/255` exactly: a
+// contribution that flips in or out is a 0.4 % step in every gradient it feeds, and that — not the
+// 2^-22 value error of ex2.approx — was the whole of round 1's 2e-4 deviation on opaque surfels
+// (tests/test_grad_attribution_gpu.py). ex2.approx decides wrongly only inside a
+// relative band of ~2^-21 around the threshold; opacity * G values inside a 16x wider band are
+// recomputed with the forward's precise expf. One contribution in ~10^5 takes that path.
+constexpr float ALPHA_MIN = 1.0f / 255.0f;
+constexpr float ALPHA_BAND = ALPHA_MIN * 8e-6f;
+__device__ __forceinline__ bool near_alpha_threshold(float og) { return fabsf(og - ALPHA_MIN) < ALPHA_BAND; }
+
 __device__ __forceinline__ float rcp_approx(float x) {
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -275,7 +285,8 @@ __device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSm
         if (!__any_sync(0xffffffffu, live)) continue;
         // the backward is compared at 1e-3 relative (the reference's own atomics are unordered):
         // single-instruction ex2 / rcp approximations (2^-22 relative) are far inside that
-        const float G = PRECISE ? expf(power) : ex2_approx(power * 1.4426950408889634f);
+        float G = PRECISE ? expf(power) : ex2_approx(power * 1.4426950408889634f);
+        if (!PRECISE && live && near_alpha_threshold(q1j.y * G)) G = expf(power);
         float alpha = min(0.99f, q1j.y * G);
         live = live && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, live)) continue;
@@ -549,8 +560,15 @@ __device__ __forceinline__ void blend_bwd2_body(const BlendBwdArgs& a, BlendBwdS
         live1 = live1 && !(power.y > 0.0f) && !(power.y < q1j.z);
         if (!__any_sync(0xffffffffu, live0 || live1)) continue;
         const float2 pl = __fmul2_rn(power, bc(1.4426950408889634f));
-        const float2 G = make_float2(ex2_approx(pl.x), ex2_approx(pl.y));
-        const float2 og = __fmul2_rn(bc(q1j.y), G);
+        float2 G = make_float2(ex2_approx(pl.x), ex2_approx(pl.y));
+        float2 og = __fmul2_rn(bc(q1j.y), G);
+        {
+          const bool n0 = live0 && near_alpha_threshold(og.x), n1 = live1 && near_alpha_threshold(og.y);
+          if (__any_sync(0xffffffffu, n0 || n1)) {   // ~1e-5 of the contributions: decide exactly
+            if (n0) { G.x = expf(power.x); og.x = q1j.y * G.x; }
+            if (n1) { G.y = expf(power.y); og.y = q1j.y * G.y; }
+          }
+        }
         float2 alpha = make_float2(min(0.99f, og.x), min(0.99f, og.y));
         live0 = live0 && !(alpha.x < 1.0f / 255.0f);
         live1 = live1 && !(alpha.y < 1.0f / 255.0f);

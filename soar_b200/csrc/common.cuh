@@ -23,7 +23,8 @@ enum KernelId {
   K_TILE_RANGES, K_BLEND_FWD, K_BLEND_BWD, K_GEOM_BWD, K_KNN_BBOX, K_KNN_MORTON, K_KNN_GATHER,
   K_KNN_BOXES, K_KNN_SEARCH, K_LBS_FWD, K_LBS_BWD, K_LBS_QUERY, K_SMPLX_SHAPE, K_SMPLX_POSEDIRS,
   K_SMPLX_JOINTS, K_SMPLX_CHAIN, K_SMPLX_SKIN, K_POST_FWD, K_POST_BWD, K_LBS_QUERY_BUILD, K_ADAM_STEP, K_DENSIFY_STATS, K_DENSIFY_SELECT,
-  K_MASK_INDEX, K_ROWS_GATHER, K_SPLIT_ROWS, K_OCCGRID, K_CONTOUR_PAD, K_COUNT
+  K_MASK_INDEX, K_ROWS_GATHER, K_SPLIT_ROWS, K_OCCGRID, K_CONTOUR_PAD, K_LBS_QUERY_KEYS, K_LBS_QUERY_TAIL,
+  K_COUNT
 };
 
 class KernelScope {

@@ -21,6 +21,8 @@
 #include <float.h>
 #include <stdlib.h>
 #include "common.cuh"
+#include "layout.h"
+#include "kernels.h"
 
 namespace soar {
 
@@ -34,6 +36,12 @@ struct DI {
   float d;
   uint32_t i;
 };
+// The squared distance, spelled once with explicit roundings so that every kernel of this file
+// (brute force, per-point grid walk, cell-batched) produces the same bits for the same pair.
+__device__ __forceinline__ float lq_dist2(float px, float py, float pz, float vx, float vy, float vz) {
+  const float dx = __fsub_rn(px, vx), dy = __fsub_rn(py, vy), dz = __fsub_rn(pz, vz);
+  return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+}
 __device__ __forceinline__ bool di_less(const DI& a, const DI& b) {
   // (distance, index) lexicographic, the index breaking ties deterministically. Squared distances
   // are >= +0 and never NaN here (NaN is rejected before it is queued), so their bit patterns order
@@ -174,8 +182,7 @@ lbs_query_kernel(const float* __restrict__ points, int N, const float* __restric
         const int v = base + u * 32 + lane;
         d[u] = FLT_MAX;
         if (v < V) {
-          const float dx = px - s_x[v], dy = py - s_y[v], dz = pz - s_z[v];
-          d[u] = dx * dx + dy * dy + dz * dz;
+          d[u] = lq_dist2(px, py, pz, s_x[v], s_y[v], s_z[v]);
         }
       }
 #pragma unroll
@@ -235,6 +242,8 @@ lbs_query_kernel(const float* __restrict__ points, int N, const float* __restric
 //   LqGridHeader | sorted x[V] | y[V] | z[V] | perm[V] (sorted position -> original index) |
 //   cell_start[cells + 1]
 constexpr int LQ_MAX_CELLS = 1 << 20;
+constexpr uint32_t LQC_SENTINEL = (uint32_t)LQ_MAX_CELLS;  // sort key of a query outside the grid
+constexpr int LQC_KEY_BITS = 21;                            // cell ids < 2^20, the sentinel = 2^20
 struct LqGridHeader {
   float ox, oy, oz, h, inv_h;
   int nx, ny, nz, V, cells;
@@ -356,8 +365,7 @@ __device__ __forceinline__ void lq_offer_run(LqSel& st, int s, int e, float px, 
     const int v = base + (int)lane;
     float d = FLT_MAX;
     if (v < e) {
-      const float dx = px - s_x[v], dy = py - s_y[v], dz = pz - s_z[v];
-      d = dx * dx + dy * dy + dz * dz;
+      d = lq_dist2(px, py, pz, s_x[v], s_y[v], s_z[v]);
     }
     const bool cand = v < e && (d < st.tau || (d == st.tau && st.tau != FLT_MAX));
     const uint32_t bal = __ballot_sync(0xffffffffu, cand);
@@ -420,12 +428,19 @@ __global__ void __launch_bounds__(LQG_THREADS, 1)
 lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
                       const float* __restrict__ lbs_weights, int J, int K,
                       const float* __restrict__ bones, float* __restrict__ out_weights,
-                      float* __restrict__ out_mats) {
+                      float* __restrict__ out_mats, const uint32_t* __restrict__ tail_keys,
+                      const uint32_t* __restrict__ tail_vals) {
   const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
   const int V = g.V;
   const float* const gx = reinterpret_cast<const float*>(blob + sizeof(LqGridHeader));
   const uint32_t* const perm = reinterpret_cast<const uint32_t*>(gx + 3 * (size_t)V);
   const uint32_t* const table = perm + V;
+  // tail mode (after lbs_query_cells_kernel): only the queries whose sorted key is the sentinel —
+  // they sit at the END of the sorted list, so a CTA whose first candidate is not one has nothing to do
+  if (tail_keys != nullptr) {
+    const int first = N - 1 - (int)blockIdx.x * LQG_WARPS;
+    if (first < 0 || tail_keys[first] != LQC_SENTINEL) return;
+  }
   extern __shared__ float s_dyn[];
   float* const s_x = s_dyn;
   float* const s_y = s_x + V;
@@ -452,7 +467,13 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
   const uint32_t lt = lanemask_lt();
   const int BIG = 1 << 20;
 
-  for (int n = blockIdx.x * LQG_WARPS + warp; n < N; n += gridDim.x * LQG_WARPS) {
+  for (int it = blockIdx.x * LQG_WARPS + warp; it < N; it += gridDim.x * LQG_WARPS) {
+    int n = it;
+    if (tail_keys != nullptr) {
+      const int pos = N - 1 - it;   // from the end of the sorted list
+      if (tail_keys[pos] != LQC_SENTINEL) break;
+      n = (int)tail_vals[pos];
+    }
     const float px = points[3 * n], py = points[3 * n + 1], pz = points[3 * n + 2];
     // virtual (unclamped) cell of the point; NaN / huge coordinates land on +-BIG
     const float fx = floorf((px - g.ox) * g.inv_h), fy = floorf((py - g.oy) * g.inv_h),
@@ -504,6 +525,181 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
       prev = k;
     }
     lq_epilogue(st.best, K, n, J, lbs_weights, s_bones, wrow, out_weights, out_mats, lane);
+  }
+}
+
+// =================================================================================================
+// Cell-batched exact query (large N)
+// =================================================================================================
+// The per-point walk above spends most of its instructions enumerating the rows of the search cube
+// with one or two vertices per 32-lane step, and on a cross-lane sorting network per 32 candidates.
+// With N in the millions many queries share a grid cell, and queries of one cell share their whole
+// candidate enumeration. So: the queries are sorted by cell (one radix sort of N (cell, index)
+// pairs); a warp takes 32 consecutive sorted queries and, for every distinct cell among them, walks
+// the rings of that cell ONCE for all its lanes — each candidate vertex is one broadcast 16-byte
+// shared load — while every lane keeps ITS query's K best in a register array kept sorted by a
+// branch-free insertion network on 64-bit (distance bits, vertex index) keys. A ring ends the search
+// for a lane exactly as above (K-th distance strictly inside the searched cube); the warp goes on
+// until all its lanes are done. The winners then go through the same epilogue, lane = rank, so the
+// result is bit-identical to the brute force. Queries outside the grid (or non-finite) sort to the
+// end under a sentinel key and are served by the per-point kernel in tail mode.
+// Neighbouring queries also share most of their K weight rows: sorted by cell, those 220-byte rows
+// hit in L1 instead of costing 6.6 KB of L2 traffic per point.
+constexpr int LQC_WARPS = 16;
+constexpr int LQC_THREADS = LQC_WARPS * 32;
+constexpr int LQC_K = 30;
+constexpr unsigned long long LQC_EMPTY = ((unsigned long long)0x7f7fffffu << 32) | 0xffffffffull;
+
+__global__ void __launch_bounds__(256)
+lq_cell_keys_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
+                    uint32_t* __restrict__ keys) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
+  const float px = points[3 * n], py = points[3 * n + 1], pz = points[3 * n + 2];
+  const float fx = floorf((px - g.ox) * g.inv_h), fy = floorf((py - g.oy) * g.inv_h),
+              fz = floorf((pz - g.oz) * g.inv_h);
+  // NaN fails every comparison: outside
+  const bool inside = fx >= 0.f && fx <= (float)(g.nx - 1) && fy >= 0.f && fy <= (float)(g.ny - 1) &&
+                      fz >= 0.f && fz <= (float)(g.nz - 1);
+  keys[n] = inside ? (uint32_t)(((int)fz * g.ny + (int)fy) * g.nx + (int)fx) : LQC_SENTINEL;
+}
+
+// c < h on 64-bit keys as ONE predicate (the C++ spelling of the min / max pair compiles to two compares)
+__device__ __forceinline__ bool lqc_less(unsigned long long c, unsigned long long h) {
+  uint32_t p;
+  asm("{ .reg .pred q; setp.lt.u64 q, %1, %2; selp.u32 %0, 1, 0, q; }" : "=r"(p) : "l"(c), "l"(h));
+  return p != 0;
+}
+// Insert c into the ascending array h[0..K) (dropping the largest): new h[j] = old h[j-1] where c sorts
+// before it, c at its place, old h[j] above. Every element is formed from OLD values only (walking j
+// downwards in place), so the K steps are independent instructions, not a carry chain. Elements below
+// FROM are known to sort before c and stay.
+template <int K, int FROM>
+__device__ __forceinline__ void lqc_insert(unsigned long long (&h)[K], unsigned long long c) {
+  bool below = lqc_less(c, h[K - 1]);  // p_j = c < h[j]
+#pragma unroll
+  for (int j = K - 1; j > FROM; --j) {
+    const bool p_prev = lqc_less(c, h[j - 1]);
+    h[j] = p_prev ? h[j - 1] : (below ? c : h[j]);
+    below = p_prev;
+  }
+  h[FROM] = below ? c : h[FROM];
+}
+
+__global__ void __launch_bounds__(LQC_THREADS, 1)
+lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
+                       const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_vals,
+                       const float* __restrict__ lbs_weights, int J, const float* __restrict__ bones,
+                       float* __restrict__ out_weights, float* __restrict__ out_mats) {
+  constexpr int K = LQC_K;
+  const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
+  const int V = g.V;
+  const float* const gx = reinterpret_cast<const float*>(blob + sizeof(LqGridHeader));
+  const uint32_t* const perm = reinterpret_cast<const uint32_t*>(gx + 3 * (size_t)V);
+  const uint32_t* const table = perm + V;
+  extern __shared__ float s_dyn[];
+  float4* const s_v = reinterpret_cast<float4*>(s_dyn);          // x y z | original index bits
+  float* const s_bones = s_dyn + 4 * (size_t)V;
+  float* const s_w = s_bones + LQ_MAX_J * 12;
+
+  const int tid = threadIdx.x;
+  const uint32_t lane = tid & 31, warp = tid >> 5;
+  for (int v = tid; v < V; v += LQC_THREADS)
+    s_v[v] = make_float4(gx[v], gx[V + v], gx[2 * V + v], __uint_as_float(perm[v]));
+  if (bones != nullptr)
+    for (int i = tid; i < J * 12; i += LQC_THREADS) s_bones[i] = bones[(i / 12) * 16 + (i % 12)];
+  __syncthreads();
+  float* const wrow = s_w + warp * LQ_MAX_J;
+
+  const int n_chunks = (N + 31) / 32;
+  for (int chunk = blockIdx.x * LQC_WARPS + warp; chunk < n_chunks; chunk += gridDim.x * LQC_WARPS) {
+    const int pos = chunk * 32 + (int)lane;
+    const uint32_t key = pos < N ? sorted_keys[pos] : LQC_SENTINEL;
+    const int n = pos < N ? (int)sorted_vals[pos] : 0;
+    float px = 0.f, py = 0.f, pz = 0.f;
+    if (key != LQC_SENTINEL) { px = points[3 * n]; py = points[3 * n + 1]; pz = points[3 * n + 2]; }
+    uint32_t pending = __ballot_sync(0xffffffffu, key != LQC_SENTINEL);
+    while (pending) {
+      const int leader = __ffs(pending) - 1;
+      const uint32_t cell = __shfl_sync(0xffffffffu, key, leader);
+      const bool mine = key == cell;
+      const uint32_t group = __ballot_sync(0xffffffffu, mine);
+      pending &= ~group;
+      const int cx = (int)(cell % (uint32_t)g.nx), cyz = (int)(cell / (uint32_t)g.nx);
+      const int cy = cyz % g.ny, cz = cyz / g.ny;
+
+      unsigned long long h[K];
+#pragma unroll
+      for (int j = 0; j < K; ++j) h[j] = LQC_EMPTY;
+      bool done = !mine;
+      int prev = -1;  // half-width of the cube searched so far
+      for (int k = 1;; ++k) {
+        const int x0 = max(cx - k, 0), x1 = min(cx + k, g.nx - 1);
+        const int y0 = max(cy - k, 0), y1 = min(cy + k, g.ny - 1);
+        const int z0 = max(cz - k, 0), z1 = min(cz + k, g.nz - 1);
+        const int nyr = y1 - y0 + 1, nrows = nyr * (z1 - z0 + 1);
+        for (int r0 = 0; r0 < nrows; r0 += 32) {
+          const int r = r0 + (int)lane;
+          int as = 0, ae = 0, bs = 0, be = 0;
+          if (r < nrows) {
+            const int yy = y0 + r % nyr, zz = z0 + r / nyr;
+            const bool inner = prev >= 0 && abs(yy - cy) <= prev && abs(zz - cz) <= prev;
+            if (!inner) {
+              lq_row_range(table, g.nx, g.ny, x0, x1, yy, zz, as, ae);
+            } else {
+              lq_row_range(table, g.nx, g.ny, x0, min(cx - prev - 1, g.nx - 1), yy, zz, as, ae);
+              lq_row_range(table, g.nx, g.ny, max(cx + prev + 1, 0), x1, yy, zz, bs, be);
+            }
+          }
+          uint32_t todo = __ballot_sync(0xffffffffu, ae > as || be > bs);
+          while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+              const int s0 = __shfl_sync(0xffffffffu, half ? bs : as, src);
+              const int e0 = __shfl_sync(0xffffffffu, half ? be : ae, src);
+              for (int v = s0; v < e0; ++v) {
+                const float4 c = s_v[v];  // warp-uniform address: one broadcast
+                const float d = lq_dist2(px, py, pz, c.x, c.y, c.z);
+                // NaN distances (never for finite queries inside the grid) fail d <= FLT_MAX
+                unsigned long long cand = ((unsigned long long)__float_as_uint(d) << 32) | __float_as_uint(c.w);
+                const bool need = !done && d <= FLT_MAX && cand < h[K - 1];
+                if (!__any_sync(0xffffffffu, need)) continue;
+                cand = need ? cand : LQC_EMPTY;
+                // candidates arrive ring by ring, i.e. roughly by distance: most land in the upper half
+                if (__any_sync(0xffffffffu, lqc_less(cand, h[K / 2]))) lqc_insert<K, 0>(h, cand);
+                else lqc_insert<K, K / 2 + 1>(h, cand);
+              }
+            }
+          }
+        }
+        const bool whole = x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1;
+        if (whole) break;
+        // everything unsearched is at least k cells away along some axis from every point of the cell
+        const float reach = (float)k * g.h * 0.9999f;
+        const float tau = __uint_as_float((uint32_t)(h[K - 1] >> 32));
+        done = done || ((uint32_t)h[K - 1] != 0xffffffffu && tau < reach * reach);
+        if (__all_sync(0xffffffffu, done)) break;
+        prev = k;
+      }
+      // epilogue, one query at a time: lane r receives the r-th best of the query held by lane q
+      uint32_t rest = group;
+      while (rest) {
+        const int q = __ffs(rest) - 1;
+        rest &= rest - 1;
+        DI best;
+        best.d = FLT_MAX; best.i = 0xffffffffu;
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          const unsigned long long kj = __shfl_sync(0xffffffffu, h[j], q);
+          if ((int)lane == j) { best.d = __uint_as_float((uint32_t)(kj >> 32)); best.i = (uint32_t)kj; }
+        }
+        const int nq = __shfl_sync(0xffffffffu, n, q);
+        lq_epilogue(best, K, nq, J, lbs_weights, s_bones, wrow, out_weights, out_mats, lane);
+      }
+    }
   }
 }
 
@@ -611,12 +807,86 @@ int soar_lbs_query_weights_grid(const float* points, int32_t N, const void* grid
     KernelScope ks(K_LBS_QUERY, stream);
     if (perm_smem)
       lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
-          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats);
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats,
+          nullptr, nullptr);
     else
       lbs_query_grid_kernel<false><<<grid_dim, LQG_THREADS, smem, stream>>>(
-          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats);
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats,
+          nullptr, nullptr);
   }
   SOAR_LAUNCH_CHECK("lbs_query_grid_kernel");
+  return SOAR_OK;
+}
+
+size_t soar_lbs_query_cells_workspace_bytes(int32_t N) {
+  if (N <= 0) return 0;
+  return binning_layout((size_t)N, sort_passes(LQC_KEY_BITS)).total;
+}
+
+int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* grid, int32_t V,
+                                 const float* lbs_weights, int32_t J, int32_t K, const float* bones,
+                                 float* out_weights, float* out_mats, void* workspace,
+                                 size_t workspace_bytes, soar_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  // the batched kernel is specialised on the reference's K = 30 and keeps (vertex, index) as 16-byte
+  // shared-memory entries; anything else takes the per-point walk
+  if (K != LQC_K || V > LQG_PERM_SMEM_MAX_V || N < 32 * LQC_WARPS || workspace == nullptr)
+    return soar_lbs_query_weights_grid(points, N, grid, V, lbs_weights, J, K, bones, out_weights,
+                                       out_mats, stream_);
+  if (V <= 0 || J <= 0 || J > LQ_MAX_J) {
+    set_error("soar_lbs_query_weights_cells: bad sizes V=%d J=%d (<= %d)", V, J, LQ_MAX_J);
+    return SOAR_E_INVALID;
+  }
+  if (!points || !grid || !lbs_weights || (!out_weights && !out_mats) || (out_mats && !bones)) {
+    set_error("soar_lbs_query_weights_cells: a required pointer is NULL");
+    return SOAR_E_INVALID;
+  }
+  const int passes = sort_passes(LQC_KEY_BITS);
+  const BinningLayout BL = binning_layout((size_t)N, passes);
+  if (workspace_bytes < BL.total) {
+    set_error("soar_lbs_query_weights_cells: workspace holds %zu bytes, need %zu", workspace_bytes, BL.total);
+    return SOAR_E_WORKSPACE;
+  }
+  char* ws = reinterpret_cast<char*>(workspace);
+  uint32_t* keys[2] = {reinterpret_cast<uint32_t*>(ws + BL.keys[0]), reinterpret_cast<uint32_t*>(ws + BL.keys[1])};
+  uint32_t* vals[2] = {reinterpret_cast<uint32_t*>(ws + BL.values[0]), reinterpret_cast<uint32_t*>(ws + BL.values[1])};
+  SOAR_CUDA_TRY(cudaMemsetAsync(ws + BL.zero_begin, 0, BL.zero_bytes, stream));
+  {
+    KernelScope ks(K_LBS_QUERY_KEYS, stream);
+    lq_cell_keys_kernel<<<ceil_div(N, 256), 256, 0, stream>>>(points, N, (const unsigned char*)grid, keys[0]);
+  }
+  SOAR_LAUNCH_CHECK("lq_cell_keys_kernel");
+  int res = 0;
+  int rc = launch_radix_sort(keys, vals, (uint32_t)N, LQC_KEY_BITS, false, /*iota_values=*/true,
+                             /*have_hist=*/false, reinterpret_cast<uint32_t*>(ws + BL.ghist),
+                             reinterpret_cast<uint32_t*>(ws + BL.status), BL.n_sort_tiles, &res, stream);
+  if (rc) return rc;
+  int dev = 0, sms = 148;
+  SOAR_CUDA_TRY(cudaGetDevice(&dev));
+  SOAR_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  {
+    const size_t smem = ((size_t)4 * V + LQ_MAX_J * 12 + LQC_WARPS * LQ_MAX_J) * 4;
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    const int grid_dim = min(sms, ceil_div(ceil_div(N, 32), LQC_WARPS));
+    KernelScope ks(K_LBS_QUERY, stream);
+    lbs_query_cells_kernel<<<grid_dim, LQC_THREADS, smem, stream>>>(
+        points, N, (const unsigned char*)grid, keys[res], vals[res], lbs_weights, J, bones, out_weights,
+        out_mats);
+  }
+  SOAR_LAUNCH_CHECK("lbs_query_cells_kernel");
+  {
+    // queries outside the grid / non-finite: the per-point walk over the sentinel tail of the sorted list
+    const size_t smem = ((size_t)4 * V + LQ_MAX_J * 12 + LQG_WARPS * 64 * 2 + LQG_WARPS * LQ_MAX_J) * 4;
+    SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_grid_kernel<true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid_dim = min(sms, ceil_div(N, LQG_WARPS));
+    KernelScope ks(K_LBS_QUERY_TAIL, stream);
+    lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
+        points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats, keys[res],
+        vals[res]);
+  }
+  SOAR_LAUNCH_CHECK("lbs_query_grid_kernel (tail)");
   return SOAR_OK;
 }
 

@@ -55,7 +55,8 @@ static const char* kKernelNames[K_COUNT] = {
     "knn_morton", "knn_gather", "knn_boxes", "knn_search", "lbs_fwd", "lbs_bwd", "lbs_query",
     "smplx_shape", "smplx_posedirs", "smplx_joints", "smplx_chain", "smplx_skin", "post_fwd",
     "post_bwd", "lbs_query_build", "adam_step", "densify_stats", "densify_select",
-    "mask_index", "rows_gather", "split_rows", "occgrid_splat", "contour_padding"};
+    "mask_index", "rows_gather", "split_rows", "occgrid_splat", "contour_padding", "lbs_query_keys",
+    "lbs_query_tail"};
 
 }  // namespace soar
 

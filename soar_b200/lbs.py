@@ -102,6 +102,7 @@ class SkinWeightQuery:
             raise RuntimeError("SkinWeightQuery: lbs_weights must have one row per canonical vertex")
         self.K = int(K)
         self.brute_force = False   # True: the V-distances-per-point kernel (kept for ablation)
+        self.per_point = False     # True: always the per-point grid walk (never the cell-batched kernel)
         V = self.verts.shape[0]
         self.grid = torch.empty(_lib.soar_lbs_query_grid_bytes(V), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
@@ -128,12 +129,21 @@ class SkinWeightQuery:
                                                         self.weights.data_ptr(), J, self.K, _capi.ptr(b),
                                                         _capi.ptr(w), _capi.ptr(m), _stream()),
                             "soar_lbs_query_weights")
-            else:
+            elif self.per_point:
                 _capi.check(_lib.soar_lbs_query_weights_grid(_capi.ptr(pts), N, self.grid.data_ptr(), V,
                                                              self.weights.data_ptr(), J, self.K,
                                                              _capi.ptr(b), _capi.ptr(w), _capi.ptr(m),
                                                              _stream()),
                             "soar_lbs_query_weights_grid")
+            else:
+                # large N: queries sorted by grid cell, one ring walk per (warp, cell); the library falls
+                # back to the per-point walk by itself for small N, K != 30 or very large V
+                ws = torch.empty(_lib.soar_lbs_query_cells_workspace_bytes(N), dtype=torch.uint8, device=dev)
+                _capi.check(_lib.soar_lbs_query_weights_cells(_capi.ptr(pts), N, self.grid.data_ptr(), V,
+                                                              self.weights.data_ptr(), J, self.K,
+                                                              _capi.ptr(b), _capi.ptr(w), _capi.ptr(m),
+                                                              _capi.ptr(ws), ws.numel(), _stream()),
+                            "soar_lbs_query_weights_cells")
         return w, m
 
     def __call__(self, points):

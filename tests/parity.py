@@ -76,6 +76,31 @@ def run_product(s, cot):
     return out, grads
 
 
+def run_product_pybind(s, cot):
+    """The same through the pybind-level entry points (`_C.rasterize_gaussians` / `_backward`, the
+    signatures of DGR/rasterize_points.h:18-50), which — like the reference's — accept rotations
+    TOGETHER with cov3D_precomp (only the python facade forbids the combination). It is the only way
+    the reference can run cov3D_precomp at all: forward.cu:273 reads rotations[idx] unconditionally."""
+    from diff_gaussian_rasterization import _C
+    e = torch.Tensor([])
+    opt = lambda k: s[k] if s.get(k) is not None else e
+    fwd = _C.rasterize_gaussians(
+        s["bg"], s["means3D"], opt("colors_precomp"), s["opacities"], opt("scales"), opt("rotations"),
+        s["scale_modifier"], opt("cov3D_precomp"), s["viewmatrix"], s["projmatrix"], s["prcppoint"],
+        s["patch_bbox"], s["tanfovx"], s["tanfovy"], s["image_height"], s["image_width"], opt("shs"),
+        s["sh_degree"], s["campos"], s["prefiltered"], s["render_front"], s["sort_descending"], False,
+        s["config"])
+    R, color, normal, depth, opac, radii, geom, binning, img = fwd
+    g = _C.rasterize_gaussians_backward(
+        s["bg"], s["means3D"], radii, opt("colors_precomp"), opt("scales"), opt("rotations"),
+        s["scale_modifier"], opt("cov3D_precomp"), s["viewmatrix"], s["projmatrix"], s["prcppoint"],
+        s["patch_bbox"], s["tanfovx"], s["tanfovy"], cot["color"], cot["normal"], cot["depth"],
+        cot["opac"], opt("shs"), s["sh_degree"], s["campos"], geom, R, binning, img, False, s["config"])
+    names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+    out = dict(color=color, normal=normal, depth=depth, opac=opac, radii=radii)
+    return out, dict(zip(names, g[:8]))
+
+
 def element_stats(a, b):
     """Per-element relative error of a against b over the elements of b that matter
     (|b| > SIGNIFICANT * max|b|): median / 99th percentile / max, and the share of ALL elements
@@ -128,11 +153,11 @@ def compare_grads(name, ours, ref, ref_again, pairs, tag=None):
     return rows
 
 
-def compare_with_reference(name, s, cot, private=True, grads=True):
+def compare_with_reference(name, s, cot, private=True, grads=True, pybind_level=False):
     """The whole contract for one scene. Returns (our outputs, reference outputs)."""
     ref = refdgr.RefRasterizer()
     r_out = ref.forward(s)
-    out, g = run_product(s, cot)
+    out, g = (run_product_pybind if pybind_level else run_product)(s, cot)
     # ---- integer contract: bit-exact ---------------------------------------------------
     assert torch.equal(out["radii"], r_out["radii"]), f"{name}: radii differ"
     R = None
@@ -157,6 +182,8 @@ def compare_with_reference(name, s, cot, private=True, grads=True):
         r_g2 = ref.backward(cot)  # the reference's own atomic-order noise
         pairs = ["means2D", "means3D", "opacity"]
         pairs += ["scales", "rotations"] if s.get("scales") is not None else ["cov3D"]
+        if s.get("scales") is None and s.get("rotations") is not None and bool(s["config"][0] > 0):
+            pairs.append("rotations")   # surfel normals still depend on the rotation
         pairs.append("sh" if s.get("shs") is not None else "colors")
         compare_grads(name, g, r_g, r_g2, pairs)
     ref.close()

@@ -66,7 +66,10 @@ def test_gradient_deviation_attribution(case):
     parity._log(dict(case=name, attribution={l: {k: list(v) for k, v in r.items()} for l, r in table.items()}))
     noise = table["reference-again"]
     for k in keys:
-        assert table["packed"][k][0] <= max(1e-3, 10 * noise[k][0]), f"packed: dL/d{k} {table['packed'][k][0]:.2e}"
+        # the product kernel takes the threshold decision exactly (precise expf inside a narrow band
+        # around alpha = 1/255): what is left is the 2^-22 value error of ex2.approx / rcp.approx
+        assert table["packed"][k][0] <= max(2e-5, 20 * noise[k][0]), \
+            f"packed: dL/d{k} {table['packed'][k][0]:.2e} vs noise {noise[k][0]:.2e}"
         # everything the reference does, done the reference's way, leaves only summation order
         assert table["scalar+all"][k][0] <= max(2e-5, 20 * noise[k][0]), \
             f"scalar+all: dL/d{k} {table['scalar+all'][k][0]:.2e} vs noise {noise[k][0]:.2e}"

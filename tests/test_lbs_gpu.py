@@ -187,3 +187,28 @@ def test_skin_weight_query_matches_reference_golden(name):
         err = (got - want).abs().max().item()
         print(f"[{name}] {'brute' if brute else 'grid'}: max-abs {err:.2e}")
         assert err <= 2e-6, f"{name} ({'brute' if brute else 'grid'}): {err:.2e}"
+
+
+def test_cell_batched_query_is_bit_identical_to_per_point_walk_at_2m():
+    """BASELINE config-5 size: the cell-batched kernel (queries sorted by grid cell, a warp walks a
+    cell's search cube once for all its lanes, per-lane register insertion) against the per-point
+    grid walk — every weight bit for bit, including queries outside the grid (the sentinel tail)."""
+    from soar_b200.lbs import SkinWeightQuery
+    m = synthetic.smplx_template(NB=1, seed=0)
+    N = 2_000_000
+    pts = synthetic.avatar_gaussians(N, m["v_template"], seed=0)["points"].cuda()
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    pts[:5000] += 0.5 * torch.randn(5000, 3, device="cuda", generator=gen)    # off the body, some outside the grid
+    pts[5000:5100] = 30.0 * torch.randn(100, 3, device="cuda", generator=gen)  # far outside
+    pts[5100] = float("nan")
+    q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda(), K=30)
+    fast = q(pts)
+    q.per_point = True
+    slow = q(pts)
+    same = (fast == slow) | (fast.isnan() & slow.isnan())
+    assert same.all(), f"{(~same).any(1).sum().item()} of {N} points differ"
+    bones = synthetic.skinning_problem(8, seed=3)["bones"].cuda()
+    m_slow = q.mats(pts, bones)
+    q.per_point = False
+    m_fast = q.mats(pts, bones)
+    assert ((m_fast == m_slow) | (m_fast.isnan() & m_slow.isnan())).all()

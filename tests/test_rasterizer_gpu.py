@@ -50,8 +50,13 @@ def _variant(s, kind):
     elif kind == "scale_mod_big":
         s["scale_modifier"] = 1.6
     elif kind == "cov3d":
-        s["cov3D_precomp"] = _cov3d_from_scale_rot(s["scales"], s["rotations"])
-        s["scales"] = s["rotations"] = None
+        # pybind-level call: cov3D_precomp WITH rotations, no scales — the only form of cov3D_precomp the
+        # reference survives (forward.cu:273 reads rotations[idx] unconditionally; through its python
+        # facade, which forbids the combination, cov3D_precomp is an illegal address: quirk Q19)
+        sc = s["scales"].clone()
+        sc[:, 2] = torch.where(sc[:, 2] < 0, torch.zeros_like(sc[:, 2]), sc[:, 2])   # surfels: a flat disk
+        s["cov3D_precomp"] = _cov3d_from_scale_rot(sc, s["rotations"])
+        s["scales"] = None
     elif kind is not None:
         raise KeyError(kind)
     return s
@@ -73,6 +78,7 @@ CASES = [
     ("scale_modifier_0.7", 60_000, 512, 512, 0, False, (0.0, 0.0, 0.0), False, False, "scale_mod"),
     ("scale_modifier_surfel_q2", 50_000, 512, 512, None, True, (0.0, 0.0, 0.0), True, False, "scale_mod_big"),
     ("cov3D_precomp", 40_000, 512, 384, 1, False, (0.3, 0.3, 0.3), False, False, "cov3d"),
+    ("cov3D_precomp_surfel", 40_000, 512, 384, None, True, (0.0, 0.0, 0.0), False, False, "cov3d"),
     # BASELINE config 3, the configuration every throughput figure is quoted on
     ("c3_sh3_1024_500k", 500_000, 1024, 1024, 3, False, (0.0, 0.0, 0.0), False, False, None),
 ]
@@ -87,13 +93,34 @@ def test_forward_backward_matches_reference(case):
                                   sort_descending=desc, render_front=front))
     s = _variant(s, variant)
     cot = to_device(synthetic.cotangents(W, H, seed=seed))
-    out, r_out = compare_with_reference(name, s, cot)
+    out, r_out = compare_with_reference(name, s, cot, pybind_level=variant == "cov3d")
     if P > 1000:
         assert (out["radii"] > 0).float().mean().item() > 0.05, "degenerate case: almost nothing visible"
     if variant == "patch":   # the sub-window really culls
         full = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=seed, surfel=surfel, bg=bg,
                                          sort_descending=desc, render_front=front))
         assert (out["radii"] > 0).sum().item() < (run_ours(full)[0]["radii"] > 0).sum().item()
+
+
+def test_cov3D_precomp_through_the_python_facade():
+    """GaussianRasterizer(cov3D_precomp=..., scales=None, rotations=None) — the call the reference's
+    facade allows but its kernel cannot survive (Q19). Here it renders with R = identity: bit-identical
+    to the pybind-level call with unit quaternions."""
+    from parity import run_product, run_product_pybind
+    s = to_device(synthetic.scene(20_000, 320, 240, sh_degree=1, seed=4))
+    cot = to_device(synthetic.cotangents(320, 240, seed=4))
+    s["cov3D_precomp"] = _cov3d_from_scale_rot(s["scales"], s["rotations"])
+    s["scales"] = s["rotations"] = None
+    out, g = run_product(s, cot)
+    s2 = dict(s)
+    s2["rotations"] = torch.tensor([1.0, 0.0, 0.0, 0.0], device="cuda").repeat(20_000, 1)
+    out2, g2 = run_product_pybind(s2, cot)
+    for k in ("color", "normal", "depth", "opac", "radii"):
+        assert torch.equal(out[k], out2[k]), k
+    assert (out["radii"] > 0).float().mean().item() > 0.05
+    for k in ("means3D", "cov3D", "sh", "opacity"):
+        e = (g[k] - g2[k].view_as(g[k])).abs().max().item() / max(g2[k].abs().max().item(), 1e-30)
+        assert e <= 1e-4, (k, e)   # the blend backward's reductions are unordered
 
 
 def test_empty_input():

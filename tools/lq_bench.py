@@ -11,11 +11,13 @@ q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda())
 import numpy as np
 hdr = q.grid[:64].cpu().numpy()
 print("grid h", hdr[12:16].view(np.float32), "dims", hdr[20:32].view(np.int32), "cells", hdr[36:40].view(np.int32))
-for bf in (False, True):
-    q.brute_force = bf
+for mode in ("cells", "per-point", "brute"):
+    q.brute_force = mode == "brute"
+    q.per_point = mode == "per-point"
+    bf = mode
     q(pts); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(3): w = q(pts)
     e1.record(); torch.cuda.synchronize()
-    print("brute" if bf else "grid", N, "points:", e0.elapsed_time(e1) / 3, "ms")
+    print(mode, N, "points:", e0.elapsed_time(e1) / 3, "ms")

@@ -37,7 +37,12 @@ rows = list(csv.reader(io.StringIO(out)))
 hdr = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
 H = rows[hdr]
 ci, cs = H.index("Instructions Executed"), H.index("# Samples")
-body = [r for r in rows[hdr + 1:] if len(r) == len(H)]
+body = []
+for r in rows[hdr + 1:]:
+    if r and r[0] == "Address":   # the next captured launch of the same kernel: one launch is enough
+        break
+    if len(r) == len(H):
+        body.append(r)
 if len(body) != len(lines):
     print(f"warning: {len(body)} SASS rows in the report vs {len(lines)} in the cubin", file=sys.stderr)
 agg = collections.defaultdict(lambda: [0, 0])
