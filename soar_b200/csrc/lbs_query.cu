@@ -429,7 +429,7 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
                       const float* __restrict__ lbs_weights, int J, int K,
                       const float* __restrict__ bones, float* __restrict__ out_weights,
                       float* __restrict__ out_mats, const uint32_t* __restrict__ tail_keys,
-                      const uint32_t* __restrict__ tail_vals) {
+                      const uint32_t* __restrict__ tail_vals, const uint32_t* __restrict__ redo_count) {
   const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
   const int V = g.V;
   const float* const gx = reinterpret_cast<const float*>(blob + sizeof(LqGridHeader));
@@ -440,6 +440,11 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
   if (tail_keys != nullptr) {
     const int first = N - 1 - (int)blockIdx.x * LQG_WARPS;
     if (first < 0 || tail_keys[first] != LQC_SENTINEL) return;
+  }
+  // redo mode: the queries the cell-batched kernel listed in tail_vals[0 .. *redo_count)
+  if (redo_count != nullptr) {
+    N = (int)*redo_count;
+    if ((int)blockIdx.x * LQG_WARPS >= N) return;
   }
   extern __shared__ float s_dyn[];
   float* const s_x = s_dyn;
@@ -473,6 +478,8 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
       const int pos = N - 1 - it;   // from the end of the sorted list
       if (tail_keys[pos] != LQC_SENTINEL) break;
       n = (int)tail_vals[pos];
+    } else if (redo_count != nullptr) {
+      n = (int)tail_vals[it];
     }
     const float px = points[3 * n], py = points[3 * n + 1], pz = points[3 * n + 2];
     // virtual (unclamped) cell of the point; NaN / huge coordinates land on +-BIG
@@ -565,33 +572,68 @@ lq_cell_keys_kernel(const float* __restrict__ points, int N, const unsigned char
   keys[n] = inside ? (uint32_t)(((int)fz * g.ny + (int)fy) * g.nx + (int)fx) : LQC_SENTINEL;
 }
 
-// c < h on 64-bit keys as ONE predicate (the C++ spelling of the min / max pair compiles to two compares)
-__device__ __forceinline__ bool lqc_less(unsigned long long c, unsigned long long h) {
-  uint32_t p;
-  asm("{ .reg .pred q; setp.lt.u64 q, %1, %2; selp.u32 %0, 1, 0, q; }" : "=r"(p) : "l"(c), "l"(h));
-  return p != 0;
-}
-// Insert c into the ascending array h[0..K) (dropping the largest): new h[j] = old h[j-1] where c sorts
-// before it, c at its place, old h[j] above. Every element is formed from OLD values only (walking j
-// downwards in place), so the K steps are independent instructions, not a carry chain. Elements below
-// FROM are known to sort before c and stay.
+// Insert d into the ascending array h[0..K) (dropping the largest): new h[j] = min(h[j], max(h[j-1], d)),
+// every element formed from OLD values only (walking j downwards in place), so the K steps are
+// independent FMNMX pairs, not a carry chain. Elements below FROM are known to be <= d and stay.
 template <int K, int FROM>
-__device__ __forceinline__ void lqc_insert(unsigned long long (&h)[K], unsigned long long c) {
-  bool below = lqc_less(c, h[K - 1]);  // p_j = c < h[j]
+__device__ __forceinline__ void lqc_insert(float (&h)[K], float d) {
 #pragma unroll
-  for (int j = K - 1; j > FROM; --j) {
-    const bool p_prev = lqc_less(c, h[j - 1]);
-    h[j] = p_prev ? h[j - 1] : (below ? c : h[j]);
-    below = p_prev;
-  }
-  h[FROM] = below ? c : h[FROM];
+  for (int j = K - 1; j > FROM; --j) h[j] = fminf(h[j], fmaxf(h[j - 1], d));
+  h[FROM] = fminf(h[FROM], d);
 }
+
+// enumerate the vertices of ring k around cell (cx, cy, cz) that are not in the cube of half-width prev:
+// calls f(v) for every sorted vertex position v, warp-uniformly
+template <typename F>
+__device__ __forceinline__ void lqc_walk_ring(const LqGridHeader& g, const uint32_t* __restrict__ table,
+                                              int cx, int cy, int cz, int k, int prev, uint32_t lane, F&& f) {
+  const int x0 = max(cx - k, 0), x1 = min(cx + k, g.nx - 1);
+  const int y0 = max(cy - k, 0), y1 = min(cy + k, g.ny - 1);
+  const int z0 = max(cz - k, 0), z1 = min(cz + k, g.nz - 1);
+  const int nyr = y1 - y0 + 1, nrows = nyr * (z1 - z0 + 1);
+  for (int r0 = 0; r0 < nrows; r0 += 32) {
+    const int r = r0 + (int)lane;
+    int as = 0, ae = 0, bs = 0, be = 0;
+    if (r < nrows) {
+      const int yy = y0 + r % nyr, zz = z0 + r / nyr;
+      const bool inner = prev >= 0 && abs(yy - cy) <= prev && abs(zz - cz) <= prev;
+      if (!inner) {
+        lq_row_range(table, g.nx, g.ny, x0, x1, yy, zz, as, ae);
+      } else {
+        lq_row_range(table, g.nx, g.ny, x0, min(cx - prev - 1, g.nx - 1), yy, zz, as, ae);
+        lq_row_range(table, g.nx, g.ny, max(cx + prev + 1, 0), x1, yy, zz, bs, be);
+      }
+    }
+    uint32_t todo = __ballot_sync(0xffffffffu, ae > as || be > bs);
+    while (todo) {
+      const int src = __ffs(todo) - 1;
+      todo &= todo - 1;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        const int s0 = __shfl_sync(0xffffffffu, half ? bs : as, src);
+        const int e0 = __shfl_sync(0xffffffffu, half ? be : ae, src);
+        for (int v = s0; v < e0; ++v) f(v);
+      }
+    }
+  }
+}
+
+// Two walks per cell. Walk 1 keeps, per lane, only the K smallest DISTANCES (32-bit keys: the
+// insertion is 2 instructions per element instead of 6 on (distance, index) pairs) and ends ring by
+// ring exactly like the per-point search; it yields tau = the K-th smallest distance of the lane's
+// query. Walk 2 revisits the same rings and appends every vertex with d <= tau to the lane's list in
+// shared memory (u16 sorted positions; <= K - 1 of them are strictly inside, the rest tie with tau).
+// The epilogue sorts a query's <= 32 entries by (distance, index) across the warp — the order the
+// brute force defines — and keeps the first K. A query with so many exact ties at tau that its list
+// overflows (duplicated vertices) is handed to the per-point kernel through the redo list.
+constexpr int LQC_CAP = 32;  // list entries per query
 
 __global__ void __launch_bounds__(LQC_THREADS, 1)
 lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
                        const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_vals,
                        const float* __restrict__ lbs_weights, int J, const float* __restrict__ bones,
-                       float* __restrict__ out_weights, float* __restrict__ out_mats) {
+                       float* __restrict__ out_weights, float* __restrict__ out_mats,
+                       uint32_t* __restrict__ redo_list, uint32_t* __restrict__ redo_count) {
   constexpr int K = LQC_K;
   const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
   const int V = g.V;
@@ -602,6 +644,7 @@ lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned c
   float4* const s_v = reinterpret_cast<float4*>(s_dyn);          // x y z | original index bits
   float* const s_bones = s_dyn + 4 * (size_t)V;
   float* const s_w = s_bones + LQ_MAX_J * 12;
+  unsigned short* const s_list = reinterpret_cast<unsigned short*>(s_w + LQC_WARPS * LQ_MAX_J);
 
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
@@ -611,6 +654,8 @@ lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned c
     for (int i = tid; i < J * 12; i += LQC_THREADS) s_bones[i] = bones[(i / 12) * 16 + (i % 12)];
   __syncthreads();
   float* const wrow = s_w + warp * LQ_MAX_J;
+  unsigned short* const my_list = s_list + (size_t)warp * LQC_CAP * 32;  // [slot][lane]
+  const float INF = __int_as_float(0x7f800000);
 
   const int n_chunks = (N + 31) / 32;
   for (int chunk = blockIdx.x * LQC_WARPS + warp; chunk < n_chunks; chunk += gridDim.x * LQC_WARPS) {
@@ -629,80 +674,87 @@ lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned c
       const int cx = (int)(cell % (uint32_t)g.nx), cyz = (int)(cell / (uint32_t)g.nx);
       const int cy = cyz % g.ny, cz = cyz / g.ny;
 
-      unsigned long long h[K];
+      // ---- walk 1: the K smallest distances ---------------------------------------------------
+      float tau;
+      int k_last;
+      {
+        float h[K];
 #pragma unroll
-      for (int j = 0; j < K; ++j) h[j] = LQC_EMPTY;
-      bool done = !mine;
-      int prev = -1;  // half-width of the cube searched so far
-      for (int k = 1;; ++k) {
-        const int x0 = max(cx - k, 0), x1 = min(cx + k, g.nx - 1);
-        const int y0 = max(cy - k, 0), y1 = min(cy + k, g.ny - 1);
-        const int z0 = max(cz - k, 0), z1 = min(cz + k, g.nz - 1);
-        const int nyr = y1 - y0 + 1, nrows = nyr * (z1 - z0 + 1);
-        for (int r0 = 0; r0 < nrows; r0 += 32) {
-          const int r = r0 + (int)lane;
-          int as = 0, ae = 0, bs = 0, be = 0;
-          if (r < nrows) {
-            const int yy = y0 + r % nyr, zz = z0 + r / nyr;
-            const bool inner = prev >= 0 && abs(yy - cy) <= prev && abs(zz - cz) <= prev;
-            if (!inner) {
-              lq_row_range(table, g.nx, g.ny, x0, x1, yy, zz, as, ae);
-            } else {
-              lq_row_range(table, g.nx, g.ny, x0, min(cx - prev - 1, g.nx - 1), yy, zz, as, ae);
-              lq_row_range(table, g.nx, g.ny, max(cx + prev + 1, 0), x1, yy, zz, bs, be);
-            }
-          }
-          uint32_t todo = __ballot_sync(0xffffffffu, ae > as || be > bs);
-          while (todo) {
-            const int src = __ffs(todo) - 1;
-            todo &= todo - 1;
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-              const int s0 = __shfl_sync(0xffffffffu, half ? bs : as, src);
-              const int e0 = __shfl_sync(0xffffffffu, half ? be : ae, src);
-              for (int v = s0; v < e0; ++v) {
-                const float4 c = s_v[v];  // warp-uniform address: one broadcast
-                const float d = lq_dist2(px, py, pz, c.x, c.y, c.z);
-                // NaN distances (never for finite queries inside the grid) fail d <= FLT_MAX
-                unsigned long long cand = ((unsigned long long)__float_as_uint(d) << 32) | __float_as_uint(c.w);
-                const bool need = !done && d <= FLT_MAX && cand < h[K - 1];
-                if (!__any_sync(0xffffffffu, need)) continue;
-                cand = need ? cand : LQC_EMPTY;
-                // candidates arrive ring by ring, i.e. roughly by distance: most land in the upper half
-                if (__any_sync(0xffffffffu, lqc_less(cand, h[K / 2]))) lqc_insert<K, 0>(h, cand);
-                else lqc_insert<K, K / 2 + 1>(h, cand);
-              }
-            }
-          }
+        for (int j = 0; j < K; ++j) h[j] = INF;
+        bool done = !mine;
+        int prev = -1;  // half-width of the cube searched so far
+        int k = 1;
+        for (;; ++k) {
+          lqc_walk_ring(g, table, cx, cy, cz, k, prev, lane, [&](int v) {
+            const float4 c = s_v[v];  // warp-uniform address: one broadcast
+            float d = lq_dist2(px, py, pz, c.x, c.y, c.z);
+            // NaN distances (never for finite queries inside the grid) fail the comparison
+            const bool need = !done && d < h[K - 1];
+            if (!__any_sync(0xffffffffu, need)) return;
+            d = need ? d : INF;
+            // candidates arrive ring by ring, i.e. roughly by distance: most land in the upper half
+            if (__any_sync(0xffffffffu, d < h[K / 2])) lqc_insert<K, 0>(h, d);
+            else lqc_insert<K, K / 2 + 1>(h, d);
+          });
+          const bool whole = cx - k <= 0 && cy - k <= 0 && cz - k <= 0 && cx + k >= g.nx - 1 &&
+                             cy + k >= g.ny - 1 && cz + k >= g.nz - 1;
+          if (whole) break;
+          // everything unsearched is at least k cells away along some axis from every point of the cell
+          const float reach = (float)k * g.h * 0.9999f;
+          done = done || h[K - 1] < reach * reach;   // (INF: fewer than K found so far)
+          if (__all_sync(0xffffffffu, done)) break;
+          prev = k;
         }
-        const bool whole = x0 == 0 && y0 == 0 && z0 == 0 && x1 == g.nx - 1 && y1 == g.ny - 1 && z1 == g.nz - 1;
-        if (whole) break;
-        // everything unsearched is at least k cells away along some axis from every point of the cell
-        const float reach = (float)k * g.h * 0.9999f;
-        const float tau = __uint_as_float((uint32_t)(h[K - 1] >> 32));
-        done = done || ((uint32_t)h[K - 1] != 0xffffffffu && tau < reach * reach);
-        if (__all_sync(0xffffffffu, done)) break;
-        prev = k;
+        tau = h[K - 1];
+        k_last = k;
       }
-      // epilogue, one query at a time: lane r receives the r-th best of the query held by lane q
-      uint32_t rest = group;
+      // ---- walk 2: everything with d <= tau -----------------------------------------------------
+      int cnt = 0;
+      bool overflow = false;
+      {
+        int prev = -1;
+        for (int k = 1; k <= k_last; ++k) {
+          lqc_walk_ring(g, table, cx, cy, cz, k, prev, lane, [&](int v) {
+            const float4 c = s_v[v];
+            const float d = lq_dist2(px, py, pz, c.x, c.y, c.z);
+            if (mine && d <= tau) {
+              if (cnt < LQC_CAP) my_list[cnt * 32 + lane] = (unsigned short)v;
+              else overflow = true;
+              ++cnt;
+            }
+          });
+          prev = k;
+        }
+      }
+      if (overflow) redo_list[atomicAdd(redo_count, 1u)] = (uint32_t)n;
+      __syncwarp();
+      // ---- epilogue, one query at a time: lane r ends up with the r-th best of the query of lane q
+      uint32_t rest = group & ~__ballot_sync(0xffffffffu, overflow);
       while (rest) {
         const int q = __ffs(rest) - 1;
         rest &= rest - 1;
+        const int cq = __shfl_sync(0xffffffffu, cnt, q);
+        const float qx = __shfl_sync(0xffffffffu, px, q), qy = __shfl_sync(0xffffffffu, py, q),
+                    qz = __shfl_sync(0xffffffffu, pz, q);
         DI best;
         best.d = FLT_MAX; best.i = 0xffffffffu;
-#pragma unroll
-        for (int j = 0; j < K; ++j) {
-          const unsigned long long kj = __shfl_sync(0xffffffffu, h[j], q);
-          if ((int)lane == j) { best.d = __uint_as_float((uint32_t)(kj >> 32)); best.i = (uint32_t)kj; }
+        if ((int)lane < cq) {
+          const float4 c = s_v[my_list[lane * 32 + q]];
+          best.d = lq_dist2(qx, qy, qz, c.x, c.y, c.z);
+          best.i = __float_as_uint(c.w);
         }
+        sort32(best, lane);
         const int nq = __shfl_sync(0xffffffffu, n, q);
         lq_epilogue(best, K, nq, J, lbs_weights, s_bones, wrow, out_weights, out_mats, lane);
       }
+      __syncwarp();
     }
   }
 }
 
+static size_t lqc_smem_bytes(int V) {
+  return ((size_t)4 * V + LQ_MAX_J * 12 + LQC_WARPS * LQ_MAX_J) * 4 + (size_t)LQC_WARPS * LQC_CAP * 32 * 2;
+}
 static size_t lq_smem_bytes(int V) {
   return ((size_t)3 * V + LQ_MAX_J * 12 + LQ_WARPS * 64 * 2 + LQ_WARPS * LQ_MAX_J) * 4;
 }
@@ -808,11 +860,11 @@ int soar_lbs_query_weights_grid(const float* points, int32_t N, const void* grid
     if (perm_smem)
       lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
           points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats,
-          nullptr, nullptr);
+          nullptr, nullptr, nullptr);
     else
       lbs_query_grid_kernel<false><<<grid_dim, LQG_THREADS, smem, stream>>>(
           points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats,
-          nullptr, nullptr);
+          nullptr, nullptr, nullptr);
   }
   SOAR_LAUNCH_CHECK("lbs_query_grid_kernel");
   return SOAR_OK;
@@ -830,7 +882,8 @@ int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* gri
   cudaStream_t stream = (cudaStream_t)stream_;
   // the batched kernel is specialised on the reference's K = 30 and keeps (vertex, index) as 16-byte
   // shared-memory entries; anything else takes the per-point walk
-  if (K != LQC_K || V > LQG_PERM_SMEM_MAX_V || N < 32 * LQC_WARPS || workspace == nullptr)
+  if (K != LQC_K || V > LQG_PERM_SMEM_MAX_V || lqc_smem_bytes(V) > 227 * 1024 || N < 32 * LQC_WARPS ||
+      workspace == nullptr)
     return soar_lbs_query_weights_grid(points, N, grid, V, lbs_weights, J, K, bones, out_weights,
                                        out_mats, stream_);
   if (V <= 0 || J <= 0 || J > LQ_MAX_J) {
@@ -864,29 +917,43 @@ int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* gri
   int dev = 0, sms = 148;
   SOAR_CUDA_TRY(cudaGetDevice(&dev));
   SOAR_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // the sort's free ping-pong halves hold the redo list (queries whose tie list overflowed) and its count
+  uint32_t* const redo_list = vals[res ^ 1];
+  uint32_t* const redo_count = keys[res ^ 1];
+  SOAR_CUDA_TRY(cudaMemsetAsync(redo_count, 0, sizeof(uint32_t), stream));
   {
-    const size_t smem = ((size_t)4 * V + LQ_MAX_J * 12 + LQC_WARPS * LQ_MAX_J) * 4;
+    const size_t smem = lqc_smem_bytes(V);
     SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
     const int grid_dim = min(sms, ceil_div(ceil_div(N, 32), LQC_WARPS));
     KernelScope ks(K_LBS_QUERY, stream);
     lbs_query_cells_kernel<<<grid_dim, LQC_THREADS, smem, stream>>>(
         points, N, (const unsigned char*)grid, keys[res], vals[res], lbs_weights, J, bones, out_weights,
-        out_mats);
+        out_mats, redo_list, redo_count);
   }
   SOAR_LAUNCH_CHECK("lbs_query_cells_kernel");
   {
-    // queries outside the grid / non-finite: the per-point walk over the sentinel tail of the sorted list
+    // queries outside the grid / non-finite: the per-point walk over the sentinel tail of the sorted list;
+    // then the redo list
     const size_t smem = ((size_t)4 * V + LQ_MAX_J * 12 + LQG_WARPS * 64 * 2 + LQG_WARPS * LQ_MAX_J) * 4;
     SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_grid_kernel<true>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid_dim = min(sms, ceil_div(N, LQG_WARPS));
-    KernelScope ks(K_LBS_QUERY_TAIL, stream);
-    lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
-        points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats, keys[res],
-        vals[res]);
+    {
+      KernelScope ks(K_LBS_QUERY_TAIL, stream);
+      lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats, keys[res],
+          vals[res], nullptr);
+    }
+    SOAR_LAUNCH_CHECK("lbs_query_grid_kernel (tail)");
+    {
+      KernelScope ks(K_LBS_QUERY_TAIL, stream);
+      lbs_query_grid_kernel<true><<<grid_dim, LQG_THREADS, smem, stream>>>(
+          points, N, (const unsigned char*)grid, lbs_weights, J, K, bones, out_weights, out_mats, nullptr,
+          redo_list, redo_count);
+    }
+    SOAR_LAUNCH_CHECK("lbs_query_grid_kernel (redo)");
   }
-  SOAR_LAUNCH_CHECK("lbs_query_grid_kernel (tail)");
   return SOAR_OK;
 }
 

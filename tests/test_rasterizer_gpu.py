@@ -177,3 +177,13 @@ def test_integer_state_is_reproducible_c3():
     assert out["opac"].min().item() >= 0.0 and out["opac"].max().item() <= 1.0
     vis = out["radii"] > 0
     assert (g["means3D"][~vis] == 0).all(), "culled Gaussians must get zero gradient"
+
+
+def test_large_image_13_tile_bits():
+    """2048x1536 = 12288 tiles: 14 tile-id bits, i.e. a different split of the tile sort's passes than
+    every other case here; same contract."""
+    _need_ref()
+    W, H = 2048, 1536
+    s = to_device(synthetic.scene(150_000, W, H, sh_degree=1, seed=6))
+    cot = to_device(synthetic.cotangents(W, H, seed=6))
+    compare_with_reference("big_image_2048x1536", s, cot)

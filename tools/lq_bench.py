@@ -11,7 +11,8 @@ q = SkinWeightQuery(m["v_template"].cuda(), m["lbs_weights"].cuda())
 import numpy as np
 hdr = q.grid[:64].cpu().numpy()
 print("grid h", hdr[12:16].view(np.float32), "dims", hdr[20:32].view(np.int32), "cells", hdr[36:40].view(np.int32))
-for mode in ("cells", "per-point", "brute"):
+MODES = sys.argv[2].split(",") if len(sys.argv) > 2 else ("cells", "per-point", "brute")
+for mode in MODES:
     q.brute_force = mode == "brute"
     q.per_point = mode == "per-point"
     bf = mode
