@@ -61,6 +61,10 @@ WORKLOADS = {
 }
 
 
+# streams the views of a step are spread over by default (measured: profiles/r02f_streams.txt)
+DEFAULT_STREAMS = {"c3": 2, "c4": 8, "c2": 4, "tiny": 4}
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -78,6 +82,12 @@ def parse_args():
     ap.add_argument("--no-sequential", action="store_true", help="skip the unchanged-caller figure")
     ap.add_argument("--no-gpu-baselines", action="store_true",
                     help="skip the reference distCUDA2 / torch LBS chain timed on this GPU")
+    ap.add_argument("--streams", type=int, default=-1,
+                    help="CUDA streams the views of a step are spread over (soar_b200.views.iter_views "
+                         "streams=...); 1 = one stream, -1 = the workload's default")
+    ap.add_argument("--per-view-loop", action="store_true",
+                    help="one autograd node per view (views.iter_views) instead of the batched node "
+                         "(views.rasterize_views)")
     ap.add_argument("--float-targets", action="store_true",
                     help="e2e: ship the target images as float32 (r01 protocol) instead of uint8")
     return ap.parse_args()
@@ -163,6 +173,9 @@ class Workload:
         self.P, self.W, self.H, self.deg = spec["P"], spec["W"], spec["H"], spec["deg"]
         self.device, self.rank, self.world = device, rank, world
         self.pipelined = True
+        self.streams = None   # set by main(): list of CUDA streams for the multi-view path
+        self.batched = True   # main(): False with --per-view-loop
+        self._cot_batched = {}
         self.float_targets = float_targets
         surfel = spec["cloud"] == "avatar"
         if surfel:
@@ -224,7 +237,19 @@ class Workload:
         self.cams_copied = [torch.cuda.Event() for _ in range(2)]
         self.cams_consumed = [torch.cuda.Event() for _ in range(2)]
         self.prefetched = None  # step whose first inputs are already on their way
+        # batched e2e: all targets of a step, double buffered over steps
+        self.tgt_all = [torch.empty((self.vpr, 8, self.H, self.W), dtype=self.tgt_dtype, device=device)
+                        for _ in range(2)]
+        self.tgts_copied = [torch.cuda.Event() for _ in range(2)]
+        self.tgts_consumed = [torch.cuda.Event() for _ in range(2)]
         self.loss_host = torch.zeros(1).pin_memory()
+
+    def cot_batched(self, V):
+        """[V, ...] cotangents for the batched node (every view gets its own copy in HBM)."""
+        if V not in self._cot_batched:
+            self._cot_batched[V] = {k: t.unsqueeze(0).repeat(V, *([1] * t.dim())).contiguous()
+                                    for k, t in self.cot.items()}
+        return self._cot_batched[V]
 
     def scene_dict(self, cam_flat):
         """Flat scene dict in the layout tests/refdgr.py and tests/util.py use."""
@@ -297,14 +322,41 @@ class SoarArm:
                   scales=p["scales"], rotations=p["rotations"])
         return self.R(st), kw
 
+    def _settings(self, cam_flat):
+        wl = self.wl
+        return self.S(image_height=wl.H, image_width=wl.W, tanfovx=wl.tanfovx, tanfovy=wl.tanfovy,
+                      bg=wl.bg, scale_modifier=1.0, viewmatrix=cam_flat[0:16].view(4, 4),
+                      projmatrix=cam_flat[16:32].view(4, 4), patch_bbox=wl.patch_bbox,
+                      prcppoint=wl.prcppoint, sh_degree=wl.deg or 0, campos=cam_flat[32:35],
+                      prefiltered=False, render_front=False, sort_descending=False, debug=False,
+                      config=wl.config)
+
+    def views_batched(self, cams):
+        """All views of a step as ONE autograd node (soar_b200.views.rasterize_views): [V, ...] images,
+        the views spread over wl.streams, gradients added in view order into the flat buffer."""
+        from soar_b200.views import rasterize_views
+        p = self.wl.params
+        return rasterize_views([self._settings(cam) for cam in cams], means3D=p["means3D"],
+                               opacities=p["opacities"], shs=p.get("shs"),
+                               colors_precomp=p.get("colors_precomp"), scales=p["scales"],
+                               rotations=p["rotations"], streams=self.wl.streams)
+
     def views_resident(self, cams):
-        """All views of a step: phase 1 of every view enqueued up front (views.iter_views),
-        gradients accumulated in place in the flat buffer (FlatGrads.direct)."""
+        """All views of a step. Default: one batched node (views_batched). --per-view-loop: phase 1 of
+        every view enqueued up front (views.iter_views), one autograd node per view. Either way the
+        gradients accumulate in place in the flat buffer (FlatGrads.direct)."""
         from soar_b200.views import iter_views
         c = self.wl.cot
+        if self.wl.batched:
+            with self.wl.flat.direct(overwrite=True):
+                color, normal, depth, opac, _ = self.views_batched(cams)
+                cb = self.wl.cot_batched(len(cams))
+                torch.autograd.backward([color, normal, depth, opac],
+                                        [cb["color"], cb["normal"], cb["depth"], cb["opac"]])
+            return
         rs, kws = zip(*(self._rasterizer(cam) for cam in cams))
         with self.wl.flat.direct(overwrite=True):   # the first view of a step stores: no zero-fill
-            for color, normal, depth, opac, _ in iter_views(rs, kws):
+            for color, normal, depth, opac, _ in iter_views(rs, kws, self.wl.streams):
                 torch.autograd.backward([color, normal, depth, opac],
                                         [c["color"], c["normal"], c["depth"], c["opac"]])
 
@@ -444,17 +496,20 @@ def step_e2e_pipelined(arm, wl, step):
 
     main.wait_event(wl.cams_copied[buf])
     pairs = (arm._rasterizer(wl.cam_all[buf][v]) for v in range(wl.vpr))  # built lazily, view by view
-    total = None
+    losses = []
     with wl.flat.direct(overwrite=True):
-        for v, (color, normal, depth, opac, _) in enumerate(iter_view_pairs(pairs)):
+        for v, (color, normal, depth, opac, _) in enumerate(iter_view_pairs(pairs, wl.streams)):
+            cur = torch.cuda.current_stream()   # the view's stream (main when wl.streams is None)
             slot = v & 1
             if v + 1 < wl.vpr:
                 stage_target(v + 1, slot ^ 1)
-            main.wait_event(wl.copied[slot])
+            cur.wait_event(wl.copied[slot])
             loss, cots = loss_and_cotangents(color, normal, depth, opac, wl.tgt_dev[slot])
             torch.autograd.backward([color, normal, depth, opac], cots)
-            wl.consumed[slot].record(main)
-            total = loss if total is None else total + loss
+            wl.consumed[slot].record(cur)
+            losses.append(loss)
+    # the views' streams have been joined: the per-view losses are summed on the caller's stream
+    total = losses[0] if len(losses) == 1 else torch.stack(losses).sum()
     wl.cams_consumed[buf].record(main)
     wl.flat.allreduce()
     _prefetch_pipelined(wl, step + 1)
@@ -463,7 +518,63 @@ def step_e2e_pipelined(arm, wl, step):
     return float(wl.loss_host[0])
 
 
+def _prefetch_batched(wl, step):
+    """Enqueue, on the copy stream, ALL inputs of step `step`: its cameras and its target images."""
+    buf = step & 1
+    with torch.cuda.stream(wl.copy_stream):
+        wl.copy_stream.wait_event(wl.cams_consumed[buf])
+        for v in range(wl.vpr):
+            wl.cam_all[buf][v].copy_(wl.cam_host[wl.view_index(step, v)], non_blocking=True)
+        wl.cams_copied[buf].record(wl.copy_stream)
+        wl.copy_stream.wait_event(wl.tgts_consumed[buf])
+        for v in range(wl.vpr):
+            wl.tgt_all[buf][v].copy_(wl.tgt_host[wl.view_index(step, v) % len(wl.tgt_host)], non_blocking=True)
+        wl.tgts_copied[buf].record(wl.copy_stream)
+    wl.prefetched = step
+
+
+def loss_and_cotangents_batched(color, normal, depth, opac, tgt):
+    """loss_and_cotangents over [V, ...] stacks: the same loss (sum over views of the four mean squared
+    errors) and the same cotangents, in one set of launches for all views."""
+    V = color.size(0)
+    if tgt.dtype == torch.uint8:
+        tgt = tgt.float() * (1.0 / 255.0)
+    loss, cots = None, []
+    for a, b in ((color, tgt[:, 0:3]), (normal, tgt[:, 3:6]), (depth, tgt[:, 6:7]), (opac, tgt[:, 7:8])):
+        d = a.detach() - b
+        part = (d * d).mean() * V
+        loss = part if loss is None else loss + part
+        cots.append(d * (2.0 * V / d.numel()))
+    return loss, cots
+
+
+def step_e2e_batched(arm, wl, step):
+    """The e2e step on the batched node: the step's cameras and target images travel on the copy
+    stream while the previous step finishes (every step still copies exactly one step's inputs inside
+    the timed region), one rasterize_views call, one loss over the [V, ...] stacks, one backward, the
+    all-reduce, the loss read back."""
+    main = torch.cuda.current_stream()
+    if wl.prefetched != step:
+        _prefetch_batched(wl, step)
+    buf = step & 1
+    main.wait_event(wl.cams_copied[buf])
+    with wl.flat.direct(overwrite=True):
+        color, normal, depth, opac, _ = arm.views_batched(wl.cam_all[buf])
+        main.wait_event(wl.tgts_copied[buf])
+        total, cots = loss_and_cotangents_batched(color, normal, depth, opac, wl.tgt_all[buf])
+        torch.autograd.backward([color, normal, depth, opac], cots)
+    wl.cams_consumed[buf].record(main)
+    wl.tgts_consumed[buf].record(main)
+    wl.flat.allreduce()
+    _prefetch_batched(wl, step + 1)
+    wl.loss_host.copy_(total.reshape(1), non_blocking=True)
+    torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
+    return float(wl.loss_host[0])
+
+
 def step_e2e(arm, wl, step):
+    if wl.pipelined and wl.batched and hasattr(arm, "views_batched"):
+        return step_e2e_batched(arm, wl, step)
     if wl.pipelined and hasattr(arm, "views_resident"):
         return step_e2e_pipelined(arm, wl, step)
     wl.flat.zero_()
@@ -549,8 +660,10 @@ def profile_pass(arm, wl, steps):
     from soar_b200 import _capi
     lib = _capi.load()
     lib.soar_prof_enable(1)
+    streams, wl.streams = wl.streams, None   # per-kernel event times need the kernels back to back on one stream
     for s in range(steps):
         step_resident(arm, wl, 1000 + s)
+    wl.streams = streams
     n = 256  # >= the library's kernel-id count (soar_prof_summary fills at most this many)
     counts = (ctypes.c_int32 * n)()
     ms = (ctypes.c_float * n)()
@@ -1090,6 +1203,12 @@ def main():
 
     wl = Workload(args.workload, device, rank, world, args.views_per_rank, float_targets=args.float_targets)
     wl.pipelined = not args.sequential
+    wl.batched = not args.per_view_loop
+    n_streams = args.streams if args.streams > 0 else DEFAULT_STREAMS.get(args.workload, 1)
+    n_streams = min(n_streams, wl.vpr)
+    if soar and wl.pipelined and n_streams > 1:
+        from soar_b200.views import view_streams
+        wl.streams = view_streams(n_streams, device)
     arm = SoarArm(wl) if soar else ReferenceArm(wl)
     Pv, R = scene_stats(wl, arm)
     lib = None
@@ -1206,8 +1325,12 @@ def main():
                        "l2": "inputs (parameters + per-view scratch) exceed the 126 MB L2; cameras cycle"
                              if args.workload == "c3" else "cameras cycle; every view re-reads parameters and "
                              "writes fresh scratch (working set per step > 126 MB L2)"},
-            "view_loop": ("phase 1 of all views of a step enqueued up front (soar_b200.views.iter_views) + "
-                          "in-place gradient accumulation (FlatGrads.direct, first view stores)")
+            "view_loop": (("all views of a step as one autograd node (soar_b200.views.rasterize_views) + "
+                           if wl.batched else
+                           "phase 1 of all views of a step enqueued up front (soar_b200.views.iter_views) + ")
+                          + "in-place gradient accumulation (FlatGrads.direct, first view stores)"
+                          + (f"; views spread over {len(wl.streams)} CUDA streams, additions in view order"
+                             if wl.streams else ""))
             if (wl.pipelined and soar) else "one blocking forward+backward per view, gradients accumulated with add_",
             "clocks": clk, "e2e": e2e, "sequential": sequential, "gpu_launches": launches,
             "allreduce": verified, "allreduce_ms": ar_ms,

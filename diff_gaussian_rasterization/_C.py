@@ -208,7 +208,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                  patchbbox, tan_fovx, tan_fovy, dL_dout_color, dL_dout_normal,
                                  dL_dout_depth, dL_dout_opac, sh, degree, campos, geomBuffer, R,
                                  binningBuffer, imageBuffer, debug, config, accumulate=None,
-                                 accumulate_store=False):
+                                 accumulate_store=False, order=None):
     """Backward. Returns (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh,
     dL_dscales, dL_drotations, dL_dviewmat, dL_dprojmat, dL_dcampos) like
     RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:107-187).
@@ -217,7 +217,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     "rotations", "cov3D" to a caller-owned float32 buffer of the gradient's shape; this view's
     gradient is then ADDED to it in place (SoarRastGrads.accumulate_mask) and the buffer itself
     is returned in the tuple. With `accumulate_store=True` the buffers are OVERWRITTEN instead (every
-    element, zeros for culled Gaussians): the first view of a step needs no zero-fill before it."""
+    element, zeros for culled Gaussians): the first view of a step needs no zero-fill before it.
+    `order` = (torch.cuda.Event or None, torch.cuda.Event): the launch that writes the gradient tensors
+    waits for the first event and records the second (soar_rast_backward_ordered), for views of one
+    step running on several streams."""
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     dev = means3D.device
@@ -274,14 +277,14 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         grads.dL_dcampos = g_campos.data_ptr()
         grads.accumulate_mask = mask
         scratch = torch.empty(_lib.soar_rast_backward_scratch_bytes(P), dtype=torch.uint8, device=dev)
-        _capi.check(_lib.soar_rast_backward(ctypes.byref(view), radii.data_ptr(),
-                                            geomBuffer.data_ptr(), binningBuffer.data_ptr(),
-                                            imageBuffer.data_ptr(), int(R),
-                                            dL_dout_color.data_ptr(), dL_dout_normal.data_ptr(),
-                                            dL_dout_depth.data_ptr(), dL_dout_opac.data_ptr(),
-                                            scratch.data_ptr(), scratch.numel(),
-                                            ctypes.byref(grads), _stream()),
-                    "rasterize_gaussians_backward")
+        after, done = order if order is not None else (None, None)
+        _capi.check(_lib.soar_rast_backward_ordered(
+            ctypes.byref(view), radii.data_ptr(), geomBuffer.data_ptr(), binningBuffer.data_ptr(),
+            imageBuffer.data_ptr(), int(R), dL_dout_color.data_ptr(), dL_dout_normal.data_ptr(),
+            dL_dout_depth.data_ptr(), dL_dout_opac.data_ptr(), scratch.data_ptr(), scratch.numel(),
+            ctypes.byref(grads), ctypes.c_void_p(after.cuda_event) if after is not None else None,
+            ctypes.c_void_p(done.cuda_event) if done is not None else None, _stream()),
+            "rasterize_gaussians_backward")
         if debug:
             torch.cuda.synchronize(dev)
     return (g_means2D, g_colors, g_opacity, g_means3D, g_cov3D, g_sh, g_scales, g_rot, g_view,

@@ -99,7 +99,8 @@ class _RasterizeGaussians(torch.autograd.Function):
                 s.tanfovy, grad_out_color, grad_out_normal, grad_out_depth, grad_out_opac, sh,
                 s.sh_degree, s.campos, geom, ctx.num_rendered, binning, img, s.debug, s.config)
         if ctx.sinks:
-            args = args + (ctx.sinks, ctx.direct is not None and ctx.direct.first_store())
+            args = args + (ctx.sinks, ctx.direct is not None and ctx.direct.first_store(),
+                           ctx.direct.order_events() if ctx.direct is not None else None)
         (g_means2D, g_colors, g_opacities, g_means3D, g_cov3D, g_sh, g_scales, g_rotations, g_view,
          g_proj, g_campos) = _call_with_snapshot(
             _C.rasterize_gaussians_backward, args, s.debug, "snapshot_bw.dump", "backward")

@@ -155,6 +155,22 @@ int soar_rast_backward(const SoarRastView* view, const int32_t* radii, const voi
                        void* scratch, size_t scratch_bytes, const SoarRastGrads* grads,
                        soar_stream_t stream);
 
+/* Extension for view loops that run several views on several streams and accumulate into the
+ * same gradient buffers (SoarRastGrads.accumulate_mask): the same backward, but the launch that
+ * writes the gradient tensors waits for `accumulate_after` (a cudaEvent_t, NULL = no wait) and
+ * `accumulated` (a cudaEvent_t, NULL = none) is recorded behind it. Chaining the views of a step
+ * through these events keeps the order of the additions — and so the rounding — fixed, and lets
+ * the first view of a step store instead of add, while the blend replays of different views
+ * still overlap. */
+typedef void* soar_event_t;
+int soar_rast_backward_ordered(const SoarRastView* view, const int32_t* radii, const void* geom,
+                               const void* binning, const void* img, uint32_t num_rendered,
+                               const float* dL_dout_color, const float* dL_dout_normal,
+                               const float* dL_dout_depth, const float* dL_dout_opac,
+                               void* scratch, size_t scratch_bytes, const SoarRastGrads* grads,
+                               soar_event_t accumulate_after, soar_event_t accumulated,
+                               soar_stream_t stream);
+
 /* Replaces `_C.mark_visible` (DGR/ext.cpp:18). The reference kernel body is
  * commented out (rasterizer_impl.cu:52-62): `present` is left untouched, so the
  * all-false tensor the caller allocated is what comes back. */

@@ -154,6 +154,12 @@ SIGNATURES = {
         [POINTER(SoarRastView), c_void_p, c_void_p, c_void_p, c_void_p, c_uint32, c_void_p,
          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, POINTER(SoarRastGrads), c_void_p],
     ),
+    "soar_rast_backward_ordered": (
+        c_int32,
+        [POINTER(SoarRastView), c_void_p, c_void_p, c_void_p, c_void_p, c_uint32, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, POINTER(SoarRastGrads), c_void_p, c_void_p,
+         c_void_p],
+    ),
     "soar_rast_mark_visible": (c_int32, [c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "soar_rast_debug_ptr": (
         c_void_p,

@@ -246,6 +246,18 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
                        const float* dL_dout_color, const float* dL_dout_normal,
                        const float* dL_dout_depth, const float* dL_dout_opac, void* scratch,
                        size_t scratch_bytes, const SoarRastGrads* grads, soar_stream_t stream_) {
+  return soar_rast_backward_ordered(v, radii, geom, binning, img, num_rendered, dL_dout_color,
+                                    dL_dout_normal, dL_dout_depth, dL_dout_opac, scratch,
+                                    scratch_bytes, grads, nullptr, nullptr, stream_);
+}
+
+int soar_rast_backward_ordered(const SoarRastView* v, const int32_t* radii, const void* geom,
+                               const void* binning, const void* img, uint32_t num_rendered,
+                               const float* dL_dout_color, const float* dL_dout_normal,
+                               const float* dL_dout_depth, const float* dL_dout_opac, void* scratch,
+                               size_t scratch_bytes, const SoarRastGrads* grads,
+                               soar_event_t accumulate_after, soar_event_t accumulated,
+                               soar_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   int rc = check_view(v, "soar_rast_backward");
   if (rc) return rc;
@@ -314,7 +326,12 @@ int soar_rast_backward(const SoarRastView* v, const int32_t* radii, const void* 
     const int mode = blend_bwd_scalar_mode();
     g.mean_direct = mode >= 0 && (mode & 4);
   }
-  return launch_geom_bwd(g, stream);
+  // the only launch that touches the gradient tensors: ordered against the other views of the step
+  if (accumulate_after) SOAR_CUDA_TRY(cudaStreamWaitEvent(stream, (cudaEvent_t)accumulate_after, 0));
+  rc = launch_geom_bwd(g, stream);
+  if (rc) return rc;
+  if (accumulated) SOAR_CUDA_TRY(cudaEventRecord((cudaEvent_t)accumulated, stream));
+  return SOAR_OK;
 }
 
 int soar_rast_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

@@ -194,3 +194,140 @@ def test_misaligned_rotation_pointers_take_the_scalar_path():
     assert rel_err(sink, grot0) <= 1e-3
     color2, _ = run(rot_odd, sink)          # accumulates a second time
     assert rel_err(sink, 2 * grot0) <= 1e-3
+
+
+@pytest.mark.parametrize("n_streams", [2, 3])
+@pytest.mark.parametrize("surfel", [False, True])
+def test_views_on_several_streams_match_the_single_stream_loop(n_streams, surfel):
+    """iter_views(streams=...): the views of a step overlap on the device. Images must be bit-identical
+    to the one-stream loop; the accumulated gradients are compared at 1e-3 relative (the blend
+    backward's per-Gaussian reductions are unordered within a view, as on one stream). The additions
+    of the views are chained through events (soar_rast_backward_ordered), and the first view stores
+    into a buffer that held garbage."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from soar_b200.views import view_streams
+    n = 5
+    scenes, cot = _views(40_000, 320, 240, n, sh_degree=2, surfel=surfel)
+    base = {k: scenes[0][k] for k in KEYS}
+
+    def step(streams, fill):
+        p = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+        flat = FlatGrads(p)
+        flat.flat.fill_(fill)
+        images = []
+        rs = [GaussianRasterizer(settings_of(s)) for s in scenes]
+        kws = [_kwargs(p) for _ in scenes]
+        with flat.direct(overwrite=True):
+            for out in iter_views(rs, kws, streams):
+                _loss(out, cot).backward()
+                images.append(out[0].detach())
+        torch.cuda.synchronize()
+        return flat, images
+
+    one, img_one = step(None, 3.0)
+    streams = view_streams(n_streams)
+    many, img_many = step(streams, -5.0)
+    for a, b in zip(img_one, img_many):
+        assert torch.equal(a, b)
+    for k in KEYS:
+        assert torch.isfinite(many.grad(k)).all()
+        assert rel_err(many.grad(k), one.grad(k)) <= 1e-3, k
+    # and again on the same streams (event pool reuse, stream re-join)
+    again, _ = step(streams, 11.0)
+    for k in KEYS:
+        assert rel_err(again.grad(k), one.grad(k)) <= 1e-3, k
+
+
+@pytest.mark.parametrize("n_streams", [0, 3])
+@pytest.mark.parametrize("surfel", [False, True])
+def test_rasterize_views_matches_the_per_view_rasterizer(n_streams, surfel):
+    """soar_b200.views.rasterize_views (all views of a step as one autograd node) against one
+    GaussianRasterizer call per view + torch.stack: images and radii bit-identical, summed parameter
+    gradients and per-view screen-space gradients at 1e-3 relative."""
+    from diff_gaussian_rasterization import GaussianRasterizer
+    from soar_b200.views import rasterize_views, view_streams
+    n = 4
+    scenes, cot = _views(30_000, 256, 208, n, sh_degree=2, surfel=surfel)
+    base = {k: scenes[0][k] for k in KEYS}
+    # per-view cotangents that differ from view to view
+    cots = [{k: v * (1.0 + 0.25 * i) for k, v in cot.items()} for i in range(n)]
+
+    ref = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    ref_out, ref_m2 = [], []
+    for s, c in zip(scenes, cots):
+        kw = _kwargs(ref)
+        out = GaussianRasterizer(settings_of(s))(**kw)
+        _loss(out, c).backward()
+        ref_out.append([t.detach() for t in out])
+        ref_m2.append(kw["means2D"].grad.clone())
+
+    got = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    m2 = torch.zeros((n, base["means3D"].size(0), 3), device="cuda", requires_grad=True)
+    streams = view_streams(n_streams) if n_streams else None
+    color, normal, depth, opac, radii = rasterize_views(
+        [settings_of(s) for s in scenes], means3D=got["means3D"], opacities=got["opacities"], shs=got["shs"],
+        scales=got["scales"], rotations=got["rotations"], means2D=m2, streams=streams)
+    for v in range(n):
+        assert torch.equal(color[v], ref_out[v][0]) and torch.equal(normal[v], ref_out[v][1])
+        assert torch.equal(depth[v], ref_out[v][2]) and torch.equal(opac[v], ref_out[v][3])
+        assert torch.equal(radii[v], ref_out[v][4])
+    stack = lambda key: torch.stack([c[key] for c in cots])
+    torch.autograd.backward([color, normal, depth, opac],
+                            [stack("color"), stack("normal"), stack("depth"), stack("opac")])
+    torch.cuda.synchronize()
+    for k in KEYS:
+        assert rel_err(got[k].grad, ref[k].grad) <= 1e-3, k
+    for v in range(n):
+        assert rel_err(m2.grad[v], ref_m2[v]) <= 1e-3, f"means2D view {v}"
+
+
+@pytest.mark.parametrize("n_streams", [0, 2])
+def test_rasterize_views_under_direct_accumulation(n_streams):
+    """Under FlatGrads.direct(overwrite=True) the batched node stores its first view into the flat
+    buffer (which held garbage) and adds the others; a second call in the same context adds on top."""
+    from soar_b200.views import rasterize_views, view_streams
+    n = 3
+    scenes, cot = _views(20_000, 192, 160, n, sh_degree=1)
+    base = {k: scenes[0][k] for k in KEYS}
+    sts = [settings_of(s) for s in scenes]
+    stack = lambda key: torch.stack([cot[key]] * n)
+    cots = [stack("color"), stack("normal"), stack("depth"), stack("opac")]
+
+    def call(p, streams):
+        out = rasterize_views(sts, means3D=p["means3D"], opacities=p["opacities"], shs=p["shs"],
+                              scales=p["scales"], rotations=p["rotations"], streams=streams)
+        torch.autograd.backward(list(out[:4]), cots)
+
+    ref = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    call(ref, None)
+    got = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    flat = FlatGrads(got)
+    flat.flat.fill_(9.0)
+    streams = view_streams(n_streams) if n_streams else None
+    with flat.direct(overwrite=True):
+        call(got, streams)
+        torch.cuda.synchronize()
+        for k in KEYS:
+            assert rel_err(flat.grad(k), ref[k].grad) <= 1e-3, k
+        call(got, streams)
+    torch.cuda.synchronize()
+    for k in KEYS:
+        assert rel_err(flat.grad(k), 2 * ref[k].grad) <= 1e-3, k
+
+
+def test_rasterize_views_argument_errors_and_empty_cloud():
+    from soar_b200.views import rasterize_views
+    scenes, _ = _views(1_000, 64, 64, 2, sh_degree=0)
+    s = scenes[0]
+    sts = [settings_of(x) for x in scenes]
+    with pytest.raises(Exception):
+        rasterize_views(sts, means3D=s["means3D"], opacities=s["opacities"], scales=s["scales"],
+                        rotations=s["rotations"])                      # neither SHs nor colours
+    other = settings_of(s)._replace(image_height=32)
+    with pytest.raises(RuntimeError):
+        rasterize_views([sts[0], other], means3D=s["means3D"], opacities=s["opacities"], shs=s["shs"],
+                        scales=s["scales"], rotations=s["rotations"])
+    e = lambda *shape: torch.zeros(shape, device="cuda")
+    out = rasterize_views(sts, means3D=e(0, 3), opacities=e(0, 1), shs=e(0, 1, 3), scales=e(0, 3),
+                          rotations=e(0, 4))
+    assert out[0].shape == (2, 3, 64, 64) and float(out[0].abs().max()) == 0.0 and out[4].shape == (2, 0)
