@@ -53,6 +53,9 @@ WORKLOADS = {
     "c4": dict(P=100_000, W=512, H=512, deg=None, cloud="avatar", views=32,
                text="SDS multi-view step: 32 views at 512x512 of 100000 avatar surfels (config 1,1,1,0), "
                     "view-sharded, one gradient allreduce"),
+    # the rasterizer stage of configs[4] alone (static canonical avatar): both arms can run it
+    "c5r": dict(P=2_000_000, W=1920, H=1080, deg=None, cloud="avatar", views=None,
+                text="rasterizer stage of config 5: 2000000 avatar surfels (config 1,1,1,0) at 1920x1080"),
     # BASELINE configs[4]: the dance_0-shaped step through AvatarRenderer (see AvatarWorkload)
     "c5": dict(P=2_000_000, W=1920, H=1080, deg=None, cloud="avatar", views=None,
                text="dance_0-shaped step: 2000000 skinned avatar surfels at 1920x1080, per rank one video "
@@ -61,8 +64,8 @@ WORKLOADS = {
 }
 
 
-# streams the views of a step are spread over by default (measured: profiles/r02f_streams.txt)
-DEFAULT_STREAMS = {"c3": 2, "c4": 8, "c2": 4, "tiny": 4}
+# streams the views of a step are spread over by default (measured: profiles/r02g_streams_batched.txt, r02h_streams_c4.txt)
+DEFAULT_STREAMS = {"c3": 4, "c4": 8, "c2": 4, "tiny": 4, "c5r": 4}
 
 
 def parse_args():

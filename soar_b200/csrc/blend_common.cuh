@@ -74,4 +74,66 @@ __device__ __forceinline__ uint32_t tile_block_mask(const float4 q0, const float
   return mask;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The pair kernels' mask (blend_fwd2 / blend_bwd2: warp = 8x8 pixel block). Same conservative
+// question per box, asked with less arithmetic:
+//   * the minimum of the convex q over a box that does not contain its centre (d = 0) lies on a face
+//     the centre can "see": the x-face nearest to 0 when 0 is outside the box's x-range, and likewise
+//     in y. At most TWO edge minimisations per box instead of four;
+//   * four 8x8 boxes instead of eight 8x4 ones (a warp blends an 8x8 block; its bit is written to
+//     both of its 8x4 positions, so the scalar twins read the same bytes and only do a little
+//     needless work);
+//   * the rounding slack 1e-5 * mag is formed once from the tile box, which bounds every sub-box.
+// Which entries survive differs from tile_block_mask only where neither test is tight: both keep every
+// entry that can pass the exact per-pixel test, so images, n_contrib and gradients do not depend on
+// the choice (tests/test_blend_twins_gpu.py runs both).
+// ---------------------------------------------------------------------------------------------
+struct BoxAxis {   // one axis of a box in d-space: [lo, hi], the face nearest to 0 and whether 0 is outside
+  float lo, hi, e;
+  bool vis;
+};
+__device__ __forceinline__ BoxAxis box_axis(float hi, float len) {
+  BoxAxis a;
+  a.hi = hi;
+  a.lo = hi - len;
+  a.vis = a.lo > 0.f || a.hi < 0.f;
+  a.e = a.lo > 0.f ? a.lo : a.hi;
+  return a;
+}
+// min of q over the box (x, y), +inf-free: returns 0 when the centre is inside
+__device__ __forceinline__ float box_qmin(float A, float B2, float C, float nBoverC, float nBoverA,
+                                          const BoxAxis& x, const BoxAxis& y) {
+  // x-face at dx = x.e: q = A e^2 + (2B e + C t) t, t = clamp(-B/C e, y.lo, y.hi)
+  const float ty = fminf(fmaxf(nBoverC * x.e, y.lo), y.hi);
+  const float vx = A * x.e * x.e + (B2 * x.e + C * ty) * ty;
+  const float tx = fminf(fmaxf(nBoverA * y.e, x.lo), x.hi);
+  const float vy = C * y.e * y.e + (B2 * y.e + A * tx) * tx;
+  const float big = 3.0e38f;
+  const float q = fminf(x.vis ? vx : big, y.vis ? vy : big);
+  return (x.vis || y.vis) ? q : 0.f;
+}
+
+// 8-bit mask in tile_block_mask's bit layout, each 8x8 block's decision written to both of its bits.
+__device__ __forceinline__ uint32_t tile_block_mask_pairs(const float4 q0, const float4 q1, float tile_px,
+                                                          float tile_py) {
+  const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
+  const float det = A * C - B * B;
+  if (!(A > 0.f && C > 0.f && det > 0.f)) return 0xffu;
+  const float gx = q0.x - tile_px, gy = q0.y - tile_py;  // centre relative to the tile origin
+  const float nBoverC = __fdividef(-B, C), nBoverA = __fdividef(-B, A), B2 = B + B;
+  const BoxAxis X = box_axis(gx, 15.f), Y = box_axis(gy, 15.f);
+  const float mx = fmaxf(fabsf(X.lo), fabsf(X.hi)), my = fmaxf(fabsf(Y.lo), fabsf(Y.hi));
+  const float mag = A * mx * mx + C * my * my + fabsf(B2) * mx * my;
+  const float lim = 2.f * (1e-5f * mag - thr);     // keep a box when qmin <= lim
+  if (box_qmin(A, B2, C, nBoverC, nBoverA, X, Y) > lim) return 0u;
+  const BoxAxis x0 = box_axis(gx, 7.f), x1 = box_axis(gx - 8.f, 7.f);
+  const BoxAxis y0 = box_axis(gy, 7.f), y1 = box_axis(gy - 8.f, 7.f);
+  uint32_t mask = 0;
+  if (!(box_qmin(A, B2, C, nBoverC, nBoverA, x0, y0) > lim)) mask |= 0x05u;        // bits 0, 2
+  if (!(box_qmin(A, B2, C, nBoverC, nBoverA, x1, y0) > lim)) mask |= 0x0au;        // bits 1, 3
+  if (!(box_qmin(A, B2, C, nBoverC, nBoverA, x0, y1) > lim)) mask |= 0x50u;        // bits 4, 6
+  if (!(box_qmin(A, B2, C, nBoverC, nBoverA, x1, y1) > lim)) mask |= 0xa0u;        // bits 5, 7
+  return mask;
+}
+
 }  // namespace soar
