@@ -83,6 +83,19 @@ class AvatarRenderer:
         front view = ascending depth order; the back-normal pass of gaussian_batch_renderer.py:167
         passes render_front=False. patch_bbox: (h0, w0, h1, w1) as camera.random_patch() returns it
         (:182); None = the whole image."""
+        return self.render_finish(self.render_begin(
+            points, rot, weights, bones, colors, scale2d, occ, camera, bg_color, sds_view, scaling_modifier,
+            render_occ, screenspace_points, render_front, patch_bbox))
+
+    def render_begin(self, points, rot, weights, bones, colors, scale2d, occ, camera: AvatarCamera,
+                     bg_color, sds_view=False, scaling_modifier=1.0, render_occ=True,
+                     screenspace_points: Optional[torch.Tensor] = None, render_front=True,
+                     patch_bbox: Optional[torch.Tensor] = None):
+        """First half of render(): skinning and the first phase (preprocess, depth order, tile counts)
+        of BOTH rasterizer passes are enqueued on the current stream without waiting for the device
+        (GaussianRasterizer.begin). A step that renders several views calls render_begin for all of
+        them (each under its own stream if it wants them to overlap) before the first render_finish:
+        the host then never sits in a num_rendered read-back with nothing queued behind it."""
         rot = torch.nn.functional.normalize(rot, dim=-1)                                  # :74
         means3D, rotations, _ = skin_gaussians(points, rot, weights, bones, swizzle=sds_view)
         if screenspace_points is None:                                                    # :155-164
@@ -103,17 +116,27 @@ class AvatarRenderer:
         scales = scale2d.repeat(1, 3)
         scales[..., -1] = -1e10                                                            # :239 (Q7)
         ones = torch.ones((points.shape[0], 1), dtype=torch.float32, device=points.device)
-        image, normal, depth, opac, radii = rasterizer(
-            means3D=means3D, means2D=screenspace_points, shs=None, colors_precomp=colors,
-            opacities=ones, scales=scales, rotations=rotations, cov3D_precomp=None)       # :254-263
-        rendered_occ = None
+        main_kw = dict(means3D=means3D, means2D=screenspace_points, shs=None, colors_precomp=colors,
+                       opacities=ones, scales=scales, rotations=rotations, cov3D_precomp=None)
+        rasterizer.begin(**main_kw)
+        occ_pass = None
         if render_occ:                                                                     # :281-291
             rasterizer_occ = GaussianRasterizer(GaussianRasterizationSettings(
                 render_front=True, sort_descending=False, **common))
-            rendered_occ = rasterizer_occ(
-                means3D=means3D.detach(), means2D=screenspace_points.detach(), shs=None,
-                colors_precomp=occ.repeat(1, 3), opacities=ones, scales=scales.detach(),
-                rotations=rotations.detach(), cov3D_precomp=None)[0]
+            occ_kw = dict(means3D=means3D.detach(), means2D=screenspace_points.detach(), shs=None,
+                          colors_precomp=occ.repeat(1, 3), opacities=ones, scales=scales.detach(),
+                          rotations=rotations.detach(), cov3D_precomp=None)
+            rasterizer_occ.begin(**occ_kw)
+            occ_pass = (rasterizer_occ, occ_kw)
+        return (rasterizer, main_kw, occ_pass, camera, screenspace_points)
+
+    def render_finish(self, pending):
+        """Second half of render(): both passes' second phase, the post block, the return dict."""
+        rasterizer, main_kw, occ_pass, camera, screenspace_points = pending
+        image, normal, depth, opac, radii = rasterizer(**main_kw)                          # :254-263
+        rendered_occ = None
+        if occ_pass is not None:
+            rendered_occ = occ_pass[0](**occ_pass[1])[0]
         normal_out, curv, depth_normal, _ = surfel_postprocess(normal, depth, opac, camera)  # :292-303
         return {"render": image, "normal": normal_out, "depth": depth, "pred_normal": depth_normal,
                 "mask": opac, "occ": rendered_occ, "curv": curv,
