@@ -238,6 +238,7 @@ int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
   // the ping-pong half the sort left free holds one block-mask byte per list entry
   b.pair_mask = reinterpret_cast<uint8_t*>(keys[sorted ^ 1]);
   b.cfg_flags = v->config_host_flags;
+  b.num_rendered = num_rendered;
   return launch_blend_fwd(b, d.grid_y, stream);
 }
 
@@ -307,6 +308,7 @@ int soar_rast_backward_ordered(const SoarRastView* v, const int32_t* radii, cons
       b.gacc = gacc;
       b.pair_mask = reinterpret_cast<const uint8_t*>(at(binning, BL.keys[sorted ^ 1]));
       b.cfg_flags = v->config_host_flags;
+      b.num_rendered = num_rendered;
       rc = launch_blend_bwd(b, d.grid_y, stream);
       if (rc) return rc;
     }
@@ -323,7 +325,7 @@ int soar_rast_backward_ordered(const SoarRastView* v, const int32_t* radii, cons
   g.viewmatrix = v->viewmatrix; g.projmatrix = v->projmatrix; g.campos = v->campos;
   g.config = v->config; g.gacc = gacc; g.g = *grads;
   {
-    const int mode = blend_bwd_scalar_mode();
+    const int mode = blend_bwd_scalar_mode(num_rendered);
     g.mean_direct = mode >= 0 && (mode & 4);
   }
   // the only launch that touches the gradient tensors: ordered against the other views of the step

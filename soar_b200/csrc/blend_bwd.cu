@@ -703,20 +703,42 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdAr
   }
 }
 
-// SOAR_BLEND_BWD_SCALAR=<n>: run the scalar twin; n - 1 = MODE bits (1 -> MODE 0 ... 8 -> MODE 7).
-int blend_bwd_scalar_mode() {
-  const char* e = getenv("SOAR_BLEND_BWD_SCALAR");
-  if (!e) return -1;
-  const int n = atoi(e);
-  return n >= 1 && n <= 8 ? n - 1 : 0;
+// One pixel per thread, MODE 0, one instantiation per config combination picked on the host: the kernel
+// small launches take (kernels.h, blend_prefers_one_pixel_threads).
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+__global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd1_kernel_t(const BlendBwdArgs a) {
+  __shared__ BlendBwdSmem sm;
+  blend_bwd_body<SURFACE, DEPTH_DIFF, NORM_DEPTH, 0>(a, sm);
+}
+
+// Kernel choice of a launch (kernels.h): environment override, else by the size of the launch.
+int blend_prefers_one_pixel_threads(const char* var, uint32_t num_rendered) {
+  const char* e = getenv(var);
+  if (e) {
+    const int n = atoi(e);
+    if (n <= 0) return -1;
+    return n <= 8 ? n - 1 : 0;
+  }
+  return num_rendered <= BLEND_SMALL_LAUNCH_PAIRS ? 0 : -1;
+}
+int blend_bwd_scalar_mode(uint32_t num_rendered) {
+  return blend_prefers_one_pixel_threads("SOAR_BLEND_BWD_SCALAR", num_rendered);
 }
 
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream) {
   dim3 grid(a.grid_x, grid_y, 1);
   {
     KernelScope ks(K_BLEND_BWD, stream);
-    const int mode = blend_bwd_scalar_mode();
-    if (mode >= 0) {
+    const int mode = blend_bwd_scalar_mode(a.num_rendered);
+    if (mode == 0 && (a.cfg_flags & SOAR_CFG_KNOWN)) {
+      const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
+                 dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
+#define SOAR_BWD1(S, D, N) blend_bwd1_kernel_t<S, D, N><<<grid, TILE_PIX, 0, stream>>>(a)
+      if (dd) { if (norm) SOAR_BWD1(true, true, true); else SOAR_BWD1(true, true, false); }
+      else if (surface) { if (norm) SOAR_BWD1(true, false, true); else SOAR_BWD1(true, false, false); }
+      else { if (norm) SOAR_BWD1(false, false, true); else SOAR_BWD1(false, false, false); }
+#undef SOAR_BWD1
+    } else if (mode >= 0) {
       switch (mode) {
         case 0: blend_bwd_kernel<0><<<grid, TILE_PIX, 0, stream>>>(a); break;
         case 1: blend_bwd_kernel<1><<<grid, TILE_PIX, 0, stream>>>(a); break;

@@ -136,4 +136,36 @@ __device__ __forceinline__ uint32_t tile_block_mask_pairs(const float4 q0, const
   return mask;
 }
 
+// The same test refined to the eight 8x4 blocks for the one-pixel-per-thread kernels: an 8x8 box that
+// fails cannot hold an 8x4 box that passes, so only the halves of surviving 8x8 boxes are tested.
+__device__ __forceinline__ uint32_t tile_block_mask_fast(const float4 q0, const float4 q1, float tile_px,
+                                                         float tile_py) {
+  const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
+  const float det = A * C - B * B;
+  if (!(A > 0.f && C > 0.f && det > 0.f)) return 0xffu;
+  const float gx = q0.x - tile_px, gy = q0.y - tile_py;
+  const float nBoverC = __fdividef(-B, C), nBoverA = __fdividef(-B, A), B2 = B + B;
+  const BoxAxis X = box_axis(gx, 15.f), Y = box_axis(gy, 15.f);
+  const float mx = fmaxf(fabsf(X.lo), fabsf(X.hi)), my = fmaxf(fabsf(Y.lo), fabsf(Y.hi));
+  const float mag = A * mx * mx + C * my * my + fabsf(B2) * mx * my;
+  const float lim = 2.f * (1e-5f * mag - thr);
+  if (box_qmin(A, B2, C, nBoverC, nBoverA, X, Y) > lim) return 0u;
+  const BoxAxis x0 = box_axis(gx, 7.f), x1 = box_axis(gx - 8.f, 7.f);
+  uint32_t mask = 0;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {          // the two 8-row halves of the tile
+    const BoxAxis y8 = box_axis(gy - 8.f * h, 7.f);
+    const bool k0 = !(box_qmin(A, B2, C, nBoverC, nBoverA, x0, y8) > lim);
+    const bool k1 = !(box_qmin(A, B2, C, nBoverC, nBoverA, x1, y8) > lim);
+    if (k0 || k1) {
+      const BoxAxis ya = box_axis(gy - 8.f * h, 3.f), yb = box_axis(gy - 8.f * h - 4.f, 3.f);
+      if (k0 && !(box_qmin(A, B2, C, nBoverC, nBoverA, x0, ya) > lim)) mask |= 1u << (4 * h);
+      if (k1 && !(box_qmin(A, B2, C, nBoverC, nBoverA, x1, ya) > lim)) mask |= 2u << (4 * h);
+      if (k0 && !(box_qmin(A, B2, C, nBoverC, nBoverA, x0, yb) > lim)) mask |= 4u << (4 * h);
+      if (k1 && !(box_qmin(A, B2, C, nBoverC, nBoverA, x1, yb) > lim)) mask |= 8u << (4 * h);
+    }
+  }
+  return mask;
+}
+
 }  // namespace soar

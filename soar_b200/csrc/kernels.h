@@ -62,6 +62,7 @@ struct BlendFwdArgs {
   float* out_opac;
   uint8_t* pair_mask;  // [R] block mask of every staged list entry (read back by the backward)
   uint32_t cfg_flags;  // SoarRastView.config_host_flags
+  uint32_t num_rendered;
 };
 int launch_blend_fwd(const BlendFwdArgs& a, int grid_y, cudaStream_t stream);
 
@@ -82,9 +83,20 @@ struct BlendBwdArgs {
   float* gacc;
   const uint8_t* pair_mask;  // [R] written by the forward blend of the same view
   uint32_t cfg_flags;  // SoarRastView.config_host_flags
+  uint32_t num_rendered;
 };
-// -1: the packed product kernel; >= 0: the scalar twin's MODE bits (SOAR_BLEND_BWD_SCALAR, blend_bwd.cu)
-int blend_bwd_scalar_mode();
+// Which blend kernel a launch takes. Two layouts exist of each: two pixels per thread with packed f32x2
+// arithmetic (4 warps per tile, fewest instructions: best when the launch fills the GPU) and one pixel
+// per thread (8 warps per tile: a long tile list is walked by twice the warps, each with a shorter
+// chain; measured 25-35 % faster on launches too small to fill the SMs, where one tile's serial walk is
+// the critical path — 32 views of 100k avatar surfels at 512x512: 336 -> 240 us backward, 183 -> 142 us
+// forward — and 30 % more instructions when the GPU is full). Without an override the launch picks by
+// its number of (tile, Gaussian) pairs. Environment `var`: "0" = packed, n >= 1 = one pixel per thread
+// (for the backward n - 1 = its MODE bits). Returns -1 for packed, else the MODE bits.
+constexpr uint32_t BLEND_SMALL_LAUNCH_PAIRS = 1u << 20;
+int blend_prefers_one_pixel_threads(const char* var, uint32_t num_rendered);
+// the backward's choice for a launch (SOAR_BLEND_BWD_SCALAR)
+int blend_bwd_scalar_mode(uint32_t num_rendered);
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream);
 
 struct GeomBwdArgs {

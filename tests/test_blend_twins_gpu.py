@@ -1,5 +1,5 @@
 """The packed two-pixels-per-thread blend kernels (blend_fwd2 / blend_bwd2) against their scalar twins
-(selected with SOAR_BLEND_FWD_SCALAR / SOAR_BLEND_BWD_SCALAR): the forward must be bit-identical
+(forced with SOAR_BLEND_FWD_SCALAR / SOAR_BLEND_BWD_SCALAR = 0 / 1; unset, a launch picks by its size): the forward must be bit-identical
 (images, n_contrib); the backward sums the pixel pair first, so gradients agree to rounding."""
 import os
 
@@ -16,10 +16,7 @@ CASES = [c for c in T.CASES if c[0] in ("c2_sh0_512", "precomp_ragged", "surfel_
 
 def _run(s, cot, scalar):
     for k in ("SOAR_BLEND_FWD_SCALAR", "SOAR_BLEND_BWD_SCALAR"):
-        if scalar:
-            os.environ[k] = "1"
-        else:
-            os.environ.pop(k, None)
+        os.environ[k] = "1" if scalar else "0"   # unset = the launch picks by its size
     try:
         out, g = T.run_ours(s, cot)
         dbg = T.debug_tensors(s)
