@@ -88,6 +88,11 @@ __device__ __forceinline__ uint32_t tile_block_mask(const float4 q0, const float
 // entry that can pass the exact per-pixel test, so images, n_contrib and gradients do not depend on
 // the choice (tests/test_blend_twins_gpu.py runs both).
 // ---------------------------------------------------------------------------------------------
+// bounding box of the tile's pixels that can still change (see live_box_publish): the masks' first test
+// runs against it instead of the whole tile, at no extra cost
+struct LiveBox {
+  float x0, y0, w, h;   // origin (pixel coordinates inside the tile) and extent (x1 - x0, y1 - y0)
+};
 struct BoxAxis {   // one axis of a box in d-space: [lo, hi], the face nearest to 0 and whether 0 is outside
   float lo, hi, e;
   bool vis;
@@ -113,18 +118,52 @@ __device__ __forceinline__ float box_qmin(float A, float B2, float C, float nBov
   return (x.vis || y.vis) ? q : 0.f;
 }
 
+// The live box of a tile. The forward kernels drop list entries at staging time that cannot reach
+// alpha >= 1/255 at any pixel that is NOT yet done: a done pixel ignores every later entry, so such an entry
+// changes nothing (and the backward, which only replays entries before each pixel's last contributor, does
+// not need it either). On opaque surfels most of a silhouette tile is done after a few entries and the
+// box shrinks to the strip of background pixels, which almost nothing behind the surface touches: the
+// long tail of the list then costs one cheap rejection per entry instead of five box tests and a walk.
+// Each warp reduces its not-done pixels to (x0, y0, x1, y1) with four redux instructions and leaves
+// them in shared memory before the round's first barrier; every thread merges the warps' boxes after it.
+__device__ __forceinline__ void live_box_publish(uint4* slot, uint32_t lane, uint32_t x, uint32_t ylo,
+                                                 uint32_t yhi, bool any_live) {
+  // lanes with no live pixel contribute the neutral elements
+  const uint32_t x0 = __reduce_min_sync(0xffffffffu, any_live ? x : 255u);
+  const uint32_t x1 = __reduce_max_sync(0xffffffffu, any_live ? x + 1u : 0u);   // exclusive: 0 = none
+  const uint32_t y0 = __reduce_min_sync(0xffffffffu, any_live ? ylo : 255u);
+  const uint32_t y1 = __reduce_max_sync(0xffffffffu, any_live ? yhi + 1u : 0u);
+  if (lane == 0) *slot = make_uint4(x0, y0, x1, y1);
+}
+template <int NWARPS>
+__device__ __forceinline__ LiveBox live_box_merge(const uint4* slots) {
+  uint32_t x0 = 255u, y0 = 255u, x1 = 0u, y1 = 0u;
+#pragma unroll
+  for (int w = 0; w < NWARPS; ++w) {
+    const uint4 b = slots[w];
+    x0 = min(x0, b.x); y0 = min(y0, b.y); x1 = max(x1, b.z); y1 = max(y1, b.w);
+  }
+  LiveBox L;   // an empty box (the CTA is about to leave its loop) degenerates to the whole tile
+  const bool none = x1 == 0u;
+  L.x0 = none ? 0.f : (float)x0;
+  L.y0 = none ? 0.f : (float)y0;
+  L.w = none ? 15.f : (float)(x1 - 1u - x0);
+  L.h = none ? 15.f : (float)(y1 - 1u - y0);
+  return L;
+}
+
 // 8-bit mask in tile_block_mask's bit layout, each 8x8 block's decision written to both of its bits.
 __device__ __forceinline__ uint32_t tile_block_mask_pairs(const float4 q0, const float4 q1, float tile_px,
-                                                          float tile_py) {
+                                                          float tile_py, const LiveBox live) {
   const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
   const float det = A * C - B * B;
   if (!(A > 0.f && C > 0.f && det > 0.f)) return 0xffu;
   const float gx = q0.x - tile_px, gy = q0.y - tile_py;  // centre relative to the tile origin
   const float nBoverC = __fdividef(-B, C), nBoverA = __fdividef(-B, A), B2 = B + B;
-  const BoxAxis X = box_axis(gx, 15.f), Y = box_axis(gy, 15.f);
-  const float mx = fmaxf(fabsf(X.lo), fabsf(X.hi)), my = fmaxf(fabsf(Y.lo), fabsf(Y.hi));
+  const float mx = fmaxf(fabsf(gx - 15.f), fabsf(gx)), my = fmaxf(fabsf(gy - 15.f), fabsf(gy));
   const float mag = A * mx * mx + C * my * my + fabsf(B2) * mx * my;
   const float lim = 2.f * (1e-5f * mag - thr);     // keep a box when qmin <= lim
+  const BoxAxis X = box_axis(gx - live.x0, live.w), Y = box_axis(gy - live.y0, live.h);
   if (box_qmin(A, B2, C, nBoverC, nBoverA, X, Y) > lim) return 0u;
   const BoxAxis x0 = box_axis(gx, 7.f), x1 = box_axis(gx - 8.f, 7.f);
   const BoxAxis y0 = box_axis(gy, 7.f), y1 = box_axis(gy - 8.f, 7.f);
@@ -139,16 +178,16 @@ __device__ __forceinline__ uint32_t tile_block_mask_pairs(const float4 q0, const
 // The same test refined to the eight 8x4 blocks for the one-pixel-per-thread kernels: an 8x8 box that
 // fails cannot hold an 8x4 box that passes, so only the halves of surviving 8x8 boxes are tested.
 __device__ __forceinline__ uint32_t tile_block_mask_fast(const float4 q0, const float4 q1, float tile_px,
-                                                         float tile_py) {
+                                                         float tile_py, const LiveBox live) {
   const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
   const float det = A * C - B * B;
   if (!(A > 0.f && C > 0.f && det > 0.f)) return 0xffu;
   const float gx = q0.x - tile_px, gy = q0.y - tile_py;
   const float nBoverC = __fdividef(-B, C), nBoverA = __fdividef(-B, A), B2 = B + B;
-  const BoxAxis X = box_axis(gx, 15.f), Y = box_axis(gy, 15.f);
-  const float mx = fmaxf(fabsf(X.lo), fabsf(X.hi)), my = fmaxf(fabsf(Y.lo), fabsf(Y.hi));
+  const float mx = fmaxf(fabsf(gx - 15.f), fabsf(gx)), my = fmaxf(fabsf(gy - 15.f), fabsf(gy));
   const float mag = A * mx * mx + C * my * my + fabsf(B2) * mx * my;
   const float lim = 2.f * (1e-5f * mag - thr);
+  const BoxAxis X = box_axis(gx - live.x0, live.w), Y = box_axis(gy - live.y0, live.h);
   if (box_qmin(A, B2, C, nBoverC, nBoverA, X, Y) > lim) return 0u;
   const BoxAxis x0 = box_axis(gx, 7.f), x1 = box_axis(gx - 8.f, 7.f);
   uint32_t mask = 0;
