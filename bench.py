@@ -245,7 +245,12 @@ class Workload:
                         for _ in range(2)]
         self.tgts_copied = [torch.cuda.Event() for _ in range(2)]
         self.tgts_consumed = [torch.cuda.Event() for _ in range(2)]
-        self.loss_host = torch.zeros(1).pin_memory()
+        # the step's loss travels device -> host asynchronously and is read ONE step late (what a training
+        # loop's logging does): the host never drains the device between steps, every step's loss is
+        # still read inside the timed region (read_loss / flush_loss)
+        self.loss_host = [torch.zeros(1).pin_memory() for _ in range(2)]
+        self.loss_ready = [torch.cuda.Event() for _ in range(2)]
+        self.loss_pending = None
 
     def cot_batched(self, V):
         """[V, ...] cotangents for the batched node (every view gets its own copy in HBM)."""
@@ -253,6 +258,25 @@ class Workload:
             self._cot_batched[V] = {k: t.unsqueeze(0).repeat(V, *([1] * t.dim())).contiguous()
                                     for k, t in self.cot.items()}
         return self._cot_batched[V]
+
+    def read_loss(self, total, step):
+        """Enqueue the D2H copy of this step's loss; wait for and return the PREVIOUS step's."""
+        k = step & 1
+        self.loss_host[k].copy_(total.reshape(1), non_blocking=True)
+        self.loss_ready[k].record(torch.cuda.current_stream())
+        prev, self.loss_pending = self.loss_pending, k
+        if prev is None:
+            return None
+        self.loss_ready[prev].synchronize()
+        return float(self.loss_host[prev][0])
+
+    def flush_loss(self):
+        """The last step's loss (called inside the timed region, after its last step)."""
+        if self.loss_pending is None:
+            return None
+        k, self.loss_pending = self.loss_pending, None
+        self.loss_ready[k].synchronize()
+        return float(self.loss_host[k][0])
 
     def scene_dict(self, cam_flat):
         """Flat scene dict in the layout tests/refdgr.py and tests/util.py use."""
@@ -274,18 +298,26 @@ class Workload:
         return self.vpr * (35 * 4 + 8 * self.H * self.W * (4 if self.float_targets else 1))
 
 
+def _sq_err(a, b, scale_u8):
+    """d = a - b (b: float in [0,1] or image bytes, converted on the fly), sum(d*d) in one pass."""
+    if b.dtype == torch.uint8:
+        d = torch.sub(a.detach(), b, alpha=scale_u8)   # bytes -> [0, 1] inside the subtraction
+    else:
+        d = a.detach() - b
+    f = d.reshape(-1)
+    return d, torch.dot(f, f)
+
+
 def loss_and_cotangents(color, normal, depth, opac, tgt):
     """The e2e step's loss — sum of the four mean squared errors against the 8-channel target — and
     its gradients w.r.t. the four images, written once and shared by both arms (same torch launches
-    on either side of the comparison)."""
+    on either side of the comparison). Three launches per image: subtract, dot, scale in place."""
     loss, cots = None, []
-    if tgt.dtype == torch.uint8:    # image bytes -> [0, 1] on the device (one launch, both arms)
-        tgt = tgt.float() * (1.0 / 255.0)
     for a, b in ((color, tgt[0:3]), (normal, tgt[3:6]), (depth, tgt[6:7]), (opac, tgt[7:8])):
-        d = a.detach() - b
-        part = (d * d).mean()
+        d, ss = _sq_err(a, b, 1.0 / 255.0)
+        part = ss / d.numel()
         loss = part if loss is None else loss + part
-        cots.append(d * (2.0 / d.numel()))
+        cots.append(d.mul_(2.0 / d.numel()))
     return loss, cots
 
 
@@ -516,9 +548,7 @@ def step_e2e_pipelined(arm, wl, step):
     wl.cams_consumed[buf].record(main)
     wl.flat.allreduce()
     _prefetch_pipelined(wl, step + 1)
-    wl.loss_host.copy_(total.reshape(1), non_blocking=True)
-    torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
-    return float(wl.loss_host[0])
+    return wl.read_loss(total, step)   # the device->host read of the step's result (one step late)
 
 
 def _prefetch_batched(wl, step):
@@ -540,14 +570,13 @@ def loss_and_cotangents_batched(color, normal, depth, opac, tgt):
     """loss_and_cotangents over [V, ...] stacks: the same loss (sum over views of the four mean squared
     errors) and the same cotangents, in one set of launches for all views."""
     V = color.size(0)
-    if tgt.dtype == torch.uint8:
-        tgt = tgt.float() * (1.0 / 255.0)
     loss, cots = None, []
     for a, b in ((color, tgt[:, 0:3]), (normal, tgt[:, 3:6]), (depth, tgt[:, 6:7]), (opac, tgt[:, 7:8])):
-        d = a.detach() - b
-        part = (d * d).mean() * V
+        d, ss = _sq_err(a, b, 1.0 / 255.0)
+        per_view = d.numel() // V
+        part = ss / per_view
         loss = part if loss is None else loss + part
-        cots.append(d * (2.0 * V / d.numel()))
+        cots.append(d.mul_(2.0 / per_view))
     return loss, cots
 
 
@@ -570,9 +599,7 @@ def step_e2e_batched(arm, wl, step):
     wl.tgts_consumed[buf].record(main)
     wl.flat.allreduce()
     _prefetch_batched(wl, step + 1)
-    wl.loss_host.copy_(total.reshape(1), non_blocking=True)
-    torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
-    return float(wl.loss_host[0])
+    return wl.read_loss(total, step)   # the device->host read of the step's result (one step late)
 
 
 def step_e2e(arm, wl, step):
@@ -596,19 +623,19 @@ def step_e2e(arm, wl, step):
     wl.flat.allreduce()
     _stage_view(wl, step + 1, 0, 0)  # the next step's first view, same prefetch as the pipelined path
     wl.prefetched = step + 1
-    wl.loss_host.copy_(total.reshape(1), non_blocking=True)
-    torch.cuda.current_stream().synchronize()  # the device->host read of the step's result
-    return float(wl.loss_host[0])
+    return wl.read_loss(total, step)   # the device->host read of the step's result (one step late)
 
 
 def timed(fn, arm, wl, steps, warmup, world, device):
     for s in range(warmup):
         fn(arm, wl, s)
+    wl.flush_loss()
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for s in range(steps):
         fn(arm, wl, warmup + s)
+    wl.flush_loss()   # e2e: the last step's loss is read before the clock stops (no-op otherwise)
     e1.record()
     barrier(world)
     return max_over_ranks(e0.elapsed_time(e1), world, device)
@@ -1302,7 +1329,8 @@ def main():
                "h2d_bytes_per_step": wl.h2d_bytes_per_step(), "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e / args.steps,
                "targets": "float32" if args.float_targets else
-                          "uint8 (image bytes, converted to [0,1] on the device; both arms)"}
+                          "uint8 (image bytes, converted to [0,1] on the device; both arms)",
+               "loss_readback": "asynchronous D2H copy of every step's loss, read one step late (both arms)"}
 
     # the unchanged caller: one blocking GaussianRasterizer call per view, autograd accumulation
     sequential = None
