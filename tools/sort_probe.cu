@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
+#include <cub/device/device_radix_sort.cuh>   // the bar to beat only: the product never includes CUB
 #include "../soar_b200/csrc/binning.cu"
 
 namespace soar {
@@ -48,6 +49,24 @@ int main(int argc, char** argv) {
     }
     printf("n=%u bits=%d passes=%d tiles=%d probe=%d (bit0 no look-back, bit1 no ranking): %.1f us total (hist+scan+passes)\n",
            n, bits, passes, tiles, mode, best * 1e3f);
+  }
+  // ---- the bar: cub::DeviceRadixSort::SortPairs on the same (u32, u32) input, same significant bits ----
+  {
+    void* temp = nullptr; size_t temp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(temp, temp_bytes, k[0], k[1], v[0], v[1], (int)n, 0, bits);
+    cudaMalloc(&temp, temp_bytes);
+    float best = 1e9f;
+    for (int it = 0; it < 5; ++it) {
+      cudaMemcpy(k[0], hk.data(), n * 4, cudaMemcpyHostToDevice);
+      cudaMemcpy(v[0], hv.data(), n * 4, cudaMemcpyHostToDevice);
+      cudaEventRecord(e0);
+      cub::DeviceRadixSort::SortPairs(temp, temp_bytes, k[0], k[1], v[0], v[1], (int)n, 0, bits);
+      cudaEventRecord(e1);
+      cudaDeviceSynchronize();
+      float ms; cudaEventElapsedTime(&ms, e0, e1);
+      best = ms < best ? ms : best;
+    }
+    printf("n=%u bits=%d cub::DeviceRadixSort::SortPairs (CUDA 12.9): %.1f us, temp %zu bytes\n", n, bits, best * 1e3f, temp_bytes);
   }
   return 0;
 }
