@@ -18,13 +18,14 @@ namespace soar {
 
 
 // SHV: SH coefficients per Gaussian fetched with 16-byte loads (16 or 4); 0 = scalar path.
-// 128 threads x 6 CTAs/SM under an 85-register cap (28 B of spill): 768 threads of loads in flight per SM
-// instead of 512 (the uncapped build takes 89 registers).
+// 128 threads x 5 CTAs/SM (no register cap bites: the build takes 89 registers, nothing spills).
+// Measured at c3 (tools/gpu_bounds_sweep.sh): 5 CTAs 42.3 us, 6 CTAs under an 85-register cap with 28 B
+// of spill 45.4 us, 8 CTAs 51.7 us.
 // (Fetching the thread's SH row with cp.async into shared memory at kernel start, awaited only where
 // the colour is evaluated, was measured: 51 vs 46 us — not done.)
 constexpr int PP_THREADS = 128;
 template <int SHV>
-__global__ void __launch_bounds__(PP_THREADS, 6) preprocess_fwd_kernel(const PreprocessArgs a) {
+__global__ void __launch_bounds__(PP_THREADS, 5) preprocess_fwd_kernel(const PreprocessArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= a.P) return;
 
