@@ -665,7 +665,9 @@ __device__ __forceinline__ void blend_bwd2_body(const BlendBwdArgs& a, BlendBwdS
 // all-in-one kernel below, which branches on the device copy of config (backward.cu:581), serves callers
 // that only hold the device tensor; it spills (the allocator has to cover all six bodies at once).
 template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
-__global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel_t(const BlendBwdArgs a) {
+// 7 CTAs/SM (73 registers) measured 343.6 us at c3 against 358.7 at 8 (64 registers) and 350.4 at 6
+// (tools/gpu_bounds_sweep.sh): the ninth register row buys more than the eighth CTA.
+__global__ void __launch_bounds__(BWD2_THREADS, 7) blend_bwd2_kernel_t(const BlendBwdArgs a) {
   __shared__ BlendBwdSmem sm;
   blend_bwd2_body<SURFACE, DEPTH_DIFF, NORM_DEPTH>(a, sm);
 }
