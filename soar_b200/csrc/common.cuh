@@ -63,9 +63,11 @@ __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; 
 // Number of sort bits above the 32 depth bits: the reference's getHigherMsb()
 // (DGR/cuda_rasterizer/rasterizer_impl.cu:35-48) restated as "smallest b with
 // n >> b == 0" — identical for every n >= 1.
+// bits of the largest tile id, n_tiles - 1 (at least 1): 4096 tiles sort over 12 bits, not 13
 inline int tile_id_bits(uint32_t n_tiles) {
+  const uint32_t top = n_tiles > 1 ? n_tiles - 1 : 1;
   int b = 0;
-  while (b < 32 && (n_tiles >> b) != 0) ++b;
+  while (b < 32 && (top >> b) != 0) ++b;
   return b;
 }
 
