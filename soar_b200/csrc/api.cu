@@ -239,6 +239,8 @@ int soar_rast_forward_render(const SoarRastView* v, void* geom, void* binning,
   b.pair_mask = reinterpret_cast<uint8_t*>(keys[sorted ^ 1]);
   b.cfg_flags = v->config_host_flags;
   b.num_rendered = num_rendered;
+  b.n_tiles = (uint32_t)d.n_tiles;
+  b.sparse_below = 0;
   return launch_blend_fwd(b, d.grid_y, stream);
 }
 
@@ -309,6 +311,8 @@ int soar_rast_backward_ordered(const SoarRastView* v, const int32_t* radii, cons
       b.pair_mask = reinterpret_cast<const uint8_t*>(at(binning, BL.keys[sorted ^ 1]));
       b.cfg_flags = v->config_host_flags;
       b.num_rendered = num_rendered;
+      b.n_tiles = (uint32_t)d.n_tiles;
+      b.sparse_below = 0;
       rc = launch_blend_bwd(b, d.grid_y, stream);
       if (rc) return rc;
     }

@@ -598,7 +598,7 @@ int launch_radix_sort(uint32_t* keys[2], uint32_t* values[2], uint32_t n, int en
 // Tile ranges (rasterizer_impl.cu:104-124) from the sorted tile ids
 // =================================================================================
 __global__ void __launch_bounds__(256)
-tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges) {
+tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges, uint32_t n_tiles) {
   // four consecutive list entries per thread (one 16-byte load) + the entry before them
   const uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
   if (base >= L) return;
@@ -616,11 +616,14 @@ tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges)
     const uint32_t idx = base + i;
     if (idx < L) {
       const uint32_t cur = k[i];
+      // ranges[n_tiles].x counts the non-empty tiles: the blend launches pick their layout by it
       if (idx == 0) {
         ranges[cur].x = 0;
+        atomicAdd(&ranges[n_tiles].x, 1u);
       } else if (cur != prev) {
         ranges[prev].y = idx;
         ranges[cur].x = idx;
+        atomicAdd(&ranges[n_tiles].x, 1u);
       }
       if (idx == L - 1) ranges[cur].y = L;
       prev = cur;
@@ -630,11 +633,11 @@ tile_ranges_kernel(uint32_t L, const uint32_t* __restrict__ keys, uint2* ranges)
 
 int launch_tile_ranges(uint32_t L, const uint32_t* keys, uint2* ranges, int n_tiles,
                        cudaStream_t stream) {
-  SOAR_CUDA_TRY(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream));
+  SOAR_CUDA_TRY(cudaMemsetAsync(ranges, 0, ((size_t)n_tiles + 2) * sizeof(uint2), stream));
   if (L == 0) return SOAR_OK;
   {
     KernelScope ks(K_TILE_RANGES, stream);
-    tile_ranges_kernel<<<ceil_div(ceil_div((int)L, 4), 256), 256, 0, stream>>>(L, keys, ranges);
+    tile_ranges_kernel<<<ceil_div(ceil_div((int)L, 4), 256), 256, 0, stream>>>(L, keys, ranges, (uint32_t)n_tiles);
   }
   SOAR_LAUNCH_CHECK("tile_ranges_kernel");
   return SOAR_OK;

@@ -162,11 +162,11 @@ struct BlendBwdSmem {
 //              dd * (A dx + B dy), dd * (C dy + B dx) instead of being formed at flush time from the
 //              moments sum(dd dx), sum(dd dy) (BlendBwdArgs.mean_direct tells geom_bwd which it got)
 template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH, int MODE>
-__device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSmem& sm) {
+__device__ __forceinline__ void blend_bwd_body(const BlendBwdArgs& a, BlendBwdSmem& sm, uint32_t tile_x,
+                                               uint32_t tile_y) {
   constexpr bool PRECISE = MODE & 1, PER_CHANNEL = MODE & 2, MEAN_DIRECT = MODE & 4;
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31, warp = tid >> 5;
-  const uint32_t tile_x = blockIdx.x, tile_y = blockIdx.y;
   const uint32_t px = tile_x * TILE_X + pix_x_in_tile(warp, lane);
   const uint32_t py = tile_y * TILE_Y + pix_y_in_tile(warp, lane);
   const bool inside = px < (uint32_t)a.W && py < (uint32_t)a.H;
@@ -668,6 +668,7 @@ template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
 // 7 CTAs/SM (73 registers) measured 343.6 us at c3 against 358.7 at 8 (64 registers) and 350.4 at 6
 // (tools/gpu_bounds_sweep.sh): the ninth register row buys more than the eighth CTA.
 __global__ void __launch_bounds__(BWD2_THREADS, 7) blend_bwd2_kernel_t(const BlendBwdArgs a) {
+  blend_exit_if_layout_declines(a.ranges, a.n_tiles, a.sparse_below, false);
   __shared__ BlendBwdSmem sm;
   blend_bwd2_body<SURFACE, DEPTH_DIFF, NORM_DEPTH>(a, sm);
 }
@@ -679,6 +680,7 @@ __device__ __forceinline__ void blend_bwd2_pick(const BlendBwdArgs& a, BlendBwdS
 }
 
 __global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel(const BlendBwdArgs a) {
+  blend_exit_if_layout_declines(a.ranges, a.n_tiles, a.sparse_below, false);
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;
@@ -690,18 +692,19 @@ __global__ void __launch_bounds__(BWD2_THREADS, 8) blend_bwd2_kernel(const Blend
 // The scalar twin (one pixel per thread), kept for the twin tests and the attribution variants.
 template <int MODE>
 __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdArgs a) {
+  blend_exit_if_layout_declines(a.ranges, a.n_tiles, a.sparse_below, true);
   __shared__ BlendBwdSmem sm;
   const bool surface = a.config[0] > 0, per_pixel_depth = a.config[2] > 0,
              normalize_depth = a.config[1] > 0;
   if (surface && per_pixel_depth) {
-    if (normalize_depth) blend_bwd_body<true, true, true, MODE>(a, sm);
-    else blend_bwd_body<true, true, false, MODE>(a, sm);
+    if (normalize_depth) blend_bwd_body<true, true, true, MODE>(a, sm, blockIdx.x, blockIdx.y);
+    else blend_bwd_body<true, true, false, MODE>(a, sm, blockIdx.x, blockIdx.y);
   } else if (surface) {
-    if (normalize_depth) blend_bwd_body<true, false, true, MODE>(a, sm);
-    else blend_bwd_body<true, false, false, MODE>(a, sm);
+    if (normalize_depth) blend_bwd_body<true, false, true, MODE>(a, sm, blockIdx.x, blockIdx.y);
+    else blend_bwd_body<true, false, false, MODE>(a, sm, blockIdx.x, blockIdx.y);
   } else {
-    if (normalize_depth) blend_bwd_body<false, false, true, MODE>(a, sm);
-    else blend_bwd_body<false, false, false, MODE>(a, sm);
+    if (normalize_depth) blend_bwd_body<false, false, true, MODE>(a, sm, blockIdx.x, blockIdx.y);
+    else blend_bwd_body<false, false, false, MODE>(a, sm, blockIdx.x, blockIdx.y);
   }
 }
 
@@ -709,8 +712,9 @@ __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd_kernel(const BlendBwdAr
 // small launches take (kernels.h, blend_prefers_one_pixel_threads).
 template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
 __global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd1_kernel_t(const BlendBwdArgs a) {
+  blend_exit_if_layout_declines(a.ranges, a.n_tiles, a.sparse_below, true);
   __shared__ BlendBwdSmem sm;
-  blend_bwd_body<SURFACE, DEPTH_DIFF, NORM_DEPTH, 0>(a, sm);
+  blend_bwd_body<SURFACE, DEPTH_DIFF, NORM_DEPTH, 0>(a, sm, blockIdx.x, blockIdx.y);
 }
 
 // Kernel choice of a launch (kernels.h): environment override, else by the size of the launch.
@@ -723,44 +727,109 @@ int blend_prefers_one_pixel_threads(const char* var, uint32_t num_rendered) {
   }
   return num_rendered <= BLEND_SMALL_LAUNCH_PAIRS ? 0 : -1;
 }
+// Non-empty tiles at or below which a frame counts as sparse: the packed kernels' resident CTA slots
+// (8 per SM) filled less than twice. 0 = an environment override decides instead.
+uint32_t blend_sparse_threshold(const char* var) {
+  if (getenv(var)) return 0;
+  const char* t = getenv("SOAR_BLEND_SPARSE_TILES");   // experiments
+  if (t) return (uint32_t)atoi(t);
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    sms = n;
+  }
+  return (uint32_t)sms * 8u * 2u;
+}
 int blend_bwd_scalar_mode(uint32_t num_rendered) {
   return blend_prefers_one_pixel_threads("SOAR_BLEND_BWD_SCALAR", num_rendered);
 }
 
-int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream) {
+// (see blend_fwd1p_kernel_t) The counter is the .x of the second statistics slot behind the ranges.
+template <bool SURFACE, bool DEPTH_DIFF, bool NORM_DEPTH>
+__global__ void __launch_bounds__(TILE_PIX, 4) blend_bwd1p_kernel_t(const BlendBwdArgs a) {
+  blend_exit_if_layout_declines(a.ranges, a.n_tiles, a.sparse_below, true);
+  __shared__ BlendBwdSmem sm;
+  __shared__ uint32_t s_next;
+  uint32_t* const counter = const_cast<uint32_t*>(&a.ranges[a.n_tiles + 1].x);
+  for (;;) {
+    if (threadIdx.x == 0) s_next = atomicAdd(counter, 1u);
+    __syncthreads();
+    const uint32_t t = s_next;
+    __syncthreads();
+    if (t >= a.n_tiles) break;
+    blend_bwd_body<SURFACE, DEPTH_DIFF, NORM_DEPTH, 0>(a, sm, t % (uint32_t)a.grid_x, t / (uint32_t)a.grid_x);
+  }
+}
+static void launch_bwd_one_pixel_drawn(const BlendBwdArgs& a, int ctas, cudaStream_t stream) {
+  const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
+             dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
+#define SOAR_BWD1P(S, D, N) blend_bwd1p_kernel_t<S, D, N><<<ctas, TILE_PIX, 0, stream>>>(a)
+  if (dd) { if (norm) SOAR_BWD1P(true, true, true); else SOAR_BWD1P(true, true, false); }
+  else if (surface) { if (norm) SOAR_BWD1P(true, false, true); else SOAR_BWD1P(true, false, false); }
+  else { if (norm) SOAR_BWD1P(false, false, true); else SOAR_BWD1P(false, false, false); }
+#undef SOAR_BWD1P
+}
+
+static void launch_bwd_one_pixel(const BlendBwdArgs& a, dim3 grid, int mode, cudaStream_t stream) {
+  if (mode == 0 && (a.cfg_flags & SOAR_CFG_KNOWN)) {
+    const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
+               dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
+#define SOAR_BWD1(S, D, N) blend_bwd1_kernel_t<S, D, N><<<grid, TILE_PIX, 0, stream>>>(a)
+    if (dd) { if (norm) SOAR_BWD1(true, true, true); else SOAR_BWD1(true, true, false); }
+    else if (surface) { if (norm) SOAR_BWD1(true, false, true); else SOAR_BWD1(true, false, false); }
+    else { if (norm) SOAR_BWD1(false, false, true); else SOAR_BWD1(false, false, false); }
+#undef SOAR_BWD1
+    return;
+  }
+  switch (mode) {
+    case 0: blend_bwd_kernel<0><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 1: blend_bwd_kernel<1><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 2: blend_bwd_kernel<2><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 3: blend_bwd_kernel<3><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 4: blend_bwd_kernel<4><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 5: blend_bwd_kernel<5><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    case 6: blend_bwd_kernel<6><<<grid, TILE_PIX, 0, stream>>>(a); break;
+    default: blend_bwd_kernel<7><<<grid, TILE_PIX, 0, stream>>>(a); break;
+  }
+}
+static void launch_bwd_packed(const BlendBwdArgs& a, dim3 grid, cudaStream_t stream) {
+  if (a.cfg_flags & SOAR_CFG_KNOWN) {
+    const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
+               dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
+#define SOAR_BWD2(S, D, N) blend_bwd2_kernel_t<S, D, N><<<grid, BWD2_THREADS, 0, stream>>>(a)
+    if (dd) { if (norm) SOAR_BWD2(true, true, true); else SOAR_BWD2(true, true, false); }
+    else if (surface) { if (norm) SOAR_BWD2(true, false, true); else SOAR_BWD2(true, false, false); }
+    else { if (norm) SOAR_BWD2(false, false, true); else SOAR_BWD2(false, false, false); }
+#undef SOAR_BWD2
+  } else {
+    blend_bwd2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(a);
+  }
+}
+
+int launch_blend_bwd(const BlendBwdArgs& a_in, int grid_y, cudaStream_t stream) {
+  BlendBwdArgs a = a_in;
   dim3 grid(a.grid_x, grid_y, 1);
   {
     KernelScope ks(K_BLEND_BWD, stream);
     const int mode = blend_bwd_scalar_mode(a.num_rendered);
-    if (mode == 0 && (a.cfg_flags & SOAR_CFG_KNOWN)) {
-      const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
-                 dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
-#define SOAR_BWD1(S, D, N) blend_bwd1_kernel_t<S, D, N><<<grid, TILE_PIX, 0, stream>>>(a)
-      if (dd) { if (norm) SOAR_BWD1(true, true, true); else SOAR_BWD1(true, true, false); }
-      else if (surface) { if (norm) SOAR_BWD1(true, false, true); else SOAR_BWD1(true, false, false); }
-      else { if (norm) SOAR_BWD1(false, false, true); else SOAR_BWD1(false, false, false); }
-#undef SOAR_BWD1
-    } else if (mode >= 0) {
-      switch (mode) {
-        case 0: blend_bwd_kernel<0><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 1: blend_bwd_kernel<1><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 2: blend_bwd_kernel<2><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 3: blend_bwd_kernel<3><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 4: blend_bwd_kernel<4><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 5: blend_bwd_kernel<5><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        case 6: blend_bwd_kernel<6><<<grid, TILE_PIX, 0, stream>>>(a); break;
-        default: blend_bwd_kernel<7><<<grid, TILE_PIX, 0, stream>>>(a); break;
-      }
-    } else if (a.cfg_flags & SOAR_CFG_KNOWN) {
-      const bool surface = a.cfg_flags & SOAR_CFG_SURFACE, norm = a.cfg_flags & SOAR_CFG_NORMALIZE_DEPTH,
-                 dd = surface && (a.cfg_flags & SOAR_CFG_PERPIX_DEPTH);
-#define SOAR_BWD2(S, D, N) blend_bwd2_kernel_t<S, D, N><<<grid, BWD2_THREADS, 0, stream>>>(a)
-      if (dd) { if (norm) SOAR_BWD2(true, true, true); else SOAR_BWD2(true, true, false); }
-      else if (surface) { if (norm) SOAR_BWD2(true, false, true); else SOAR_BWD2(true, false, false); }
-      else { if (norm) SOAR_BWD2(false, false, true); else SOAR_BWD2(false, false, false); }
-#undef SOAR_BWD2
+    const uint32_t sparse_below = (a.cfg_flags & SOAR_CFG_KNOWN) ? blend_sparse_threshold("SOAR_BLEND_BWD_SCALAR") : 0;
+    a.sparse_below = 0;
+    if (mode >= 0) {
+      launch_bwd_one_pixel(a, grid, mode, stream);   // small launch, or forced
+    } else if (sparse_below == 0) {
+      launch_bwd_packed(a, grid, stream);            // forced
     } else {
-      blend_bwd2_kernel<<<grid, BWD2_THREADS, 0, stream>>>(a);
+      a.sparse_below = sparse_below;                 // the frame decides (kernels.h)
+      // the tile counter of the drawn launch: a backward may run more than once on one forward
+      if (cudaMemsetAsync(const_cast<uint32_t*>(&a.ranges[a.n_tiles + 1].x), 0, sizeof(uint32_t), stream) != cudaSuccess) {
+        set_error("blend_bwd: resetting the tile counter failed");
+        return SOAR_E_CUDA;
+      }
+      launch_bwd_packed(a, grid, stream);
+      launch_bwd_one_pixel_drawn(a, (int)min(a.n_tiles, sparse_below / 4u), stream);
     }
   }
   SOAR_LAUNCH_CHECK("blend_bwd_kernel");

@@ -63,6 +63,8 @@ struct BlendFwdArgs {
   uint8_t* pair_mask;  // [R] block mask of every staged list entry (read back by the backward)
   uint32_t cfg_flags;  // SoarRastView.config_host_flags
   uint32_t num_rendered;
+  uint32_t n_tiles;        // ranges[n_tiles].x = non-empty tiles of the frame (tile_ranges_kernel)
+  uint32_t sparse_below;   // set by the launcher: 0 = run; else run only if (non-empty <= this) == one-pixel layout
 };
 int launch_blend_fwd(const BlendFwdArgs& a, int grid_y, cudaStream_t stream);
 
@@ -84,6 +86,8 @@ struct BlendBwdArgs {
   const uint8_t* pair_mask;  // [R] written by the forward blend of the same view
   uint32_t cfg_flags;  // SoarRastView.config_host_flags
   uint32_t num_rendered;
+  uint32_t n_tiles;
+  uint32_t sparse_below;
 };
 // Which blend kernel a launch takes. Two layouts exist of each: two pixels per thread with packed f32x2
 // arithmetic (4 warps per tile, fewest instructions: best when the launch fills the GPU) and one pixel
@@ -95,6 +99,22 @@ struct BlendBwdArgs {
 // (for the backward n - 1 = its MODE bits). Returns -1 for packed, else the MODE bits.
 constexpr uint32_t BLEND_SMALL_LAUNCH_PAIRS = 1u << 20;
 int blend_prefers_one_pixel_threads(const char* var, uint32_t num_rendered);
+// Larger launches decide ON THE DEVICE, by how many tiles of the frame hold anything: an avatar in front of
+// an empty background is a few hundred long tiles however many pairs it has (2M surfels at 1080p: 11.8M
+// pairs in 1267 of 8160 tiles), the same latency-bound shape as a small launch. Both layouts are launched;
+// every CTA of the one that does not fit the frame returns on its first instruction (a few microseconds
+// of empty launch per frame). The threshold: the frame's non-empty tiles do not fill the packed
+// kernel's resident CTA slots twice over. Returns 0 when an environment override is in force.
+uint32_t blend_sparse_threshold(const char* var);
+// (`exit` through inline PTX rather than `return`: an early return edge made the compiler give up hoisting
+// the backward's lane-constant reduction bookkeeping out of its inner loop — 343 -> 364 us at c3.)
+__device__ __forceinline__ void blend_exit_if_layout_declines(const uint2* ranges, uint32_t n_tiles,
+                                                              uint32_t sparse_below, bool one_pixel_layout) {
+  if (sparse_below != 0) {
+    const bool sparse = ranges[n_tiles].x <= sparse_below;
+    if (sparse != one_pixel_layout) asm volatile("exit;");
+  }
+}
 // the backward's choice for a launch (SOAR_BLEND_BWD_SCALAR)
 int blend_bwd_scalar_mode(uint32_t num_rendered);
 int launch_blend_bwd(const BlendBwdArgs& a, int grid_y, cudaStream_t stream);

@@ -101,7 +101,7 @@ struct ImageLayout {
   size_t final_T;    // f32[W*H]
   size_t n_contrib;  // u32[W*H]
   size_t final_D;    // f32[W*H]
-  size_t ranges;     // uint2[tiles]
+  size_t ranges;     // uint2[tiles] + two uint2: {non-empty tiles, forward tile counter}, {backward tile counter, -}
   size_t total;
 };
 
@@ -113,7 +113,7 @@ inline ImageLayout image_layout(int W, int H) {
   L.final_T = off;   off = align_up(off + N * 4, 256);
   L.n_contrib = off; off = align_up(off + N * 4, 256);
   L.final_D = off;   off = align_up(off + N * 4, 256);
-  L.ranges = off;    off = align_up(off + tiles * 8, 256);
+  L.ranges = off;    off = align_up(off + (tiles + 2) * 8, 256);
   L.total = off + 256;
   return L;
 }
