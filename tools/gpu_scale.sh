@@ -34,3 +34,4 @@ PY
     done
   done
 done
+exit 0
