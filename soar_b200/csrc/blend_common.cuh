@@ -24,55 +24,11 @@ __device__ __forceinline__ uint32_t pix_y_in_tile(uint32_t warp, uint32_t lane) 
   return (warp >> 1) * BLK_H + (lane >> 3);
 }
 
-// q(d) = A dx^2 + 2 B dx dy + C dy^2 minimised over the box dx in [dx0,dx1], dy in [dy0,dy1]
-// (d = Gaussian centre - pixel). power = -q/2. Returns true when some pixel of the box MAY
-// pass `power >= thr_exact`; thr (REC_THR) already sits 0.02 below the exact threshold and a
-// further 1e-5 * (magnitude of the terms) absorbs the rounding of both this evaluation and
-// the kernels' own power polynomial. Non positive-definite conics and NaNs are never culled.
-__device__ __forceinline__ bool box_may_contribute(float A, float B, float C, float thr, float dx0,
-                                                   float dx1, float dy0, float dy1) {
-  const float det = A * C - B * B;
-  if (!(A > 0.f && C > 0.f && det > 0.f)) return true;
-  if (dx0 <= 0.f && dx1 >= 0.f && dy0 <= 0.f && dy1 >= 0.f) return true;  // centre inside
-  // approximate quotients are enough: evaluating q at a point 2^-22 (relative) off the edge minimiser
-  // raises it by ~1e-13 of its terms, eight orders below the 1e-5 * mag slack of the final test
-  const float nBoverC = __fdividef(-B, C), nBoverA = __fdividef(-B, A);
-  float qmin;
-  {
-    const float y0 = fminf(fmaxf(nBoverC * dx0, dy0), dy1);
-    const float y1 = fminf(fmaxf(nBoverC * dx1, dy0), dy1);
-    const float v0 = A * dx0 * dx0 + (2.f * B * dx0 + C * y0) * y0;
-    const float v1 = A * dx1 * dx1 + (2.f * B * dx1 + C * y1) * y1;
-    qmin = fminf(v0, v1);
-  }
-  {
-    const float x0 = fminf(fmaxf(nBoverA * dy0, dx0), dx1);
-    const float x1 = fminf(fmaxf(nBoverA * dy1, dx0), dx1);
-    const float v0 = C * dy0 * dy0 + (2.f * B * dy0 + A * x0) * x0;
-    const float v1 = C * dy1 * dy1 + (2.f * B * dy1 + A * x1) * x1;
-    qmin = fminf(qmin, fminf(v0, v1));
-  }
-  const float mx = fmaxf(fabsf(dx0), fabsf(dx1)), my = fmaxf(fabsf(dy0), fabsf(dy1));
-  const float mag = A * mx * mx + C * my * my + 2.f * fabsf(B) * mx * my;
-  return !(0.5f * qmin > -thr + 1e-5f * mag);
-}
-
-// 8-bit mask of the tile's 8x4 blocks a Gaussian may contribute to (bit = warp index).
-__device__ __forceinline__ uint32_t tile_block_mask(const float4 q0, const float4 q1, float tile_px,
-                                                    float tile_py) {
-  const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;
-  const float gx = q0.x - tile_px, gy = q0.y - tile_py;  // centre relative to the tile origin
-  // whole tile first: pixels 0..15 in both axes
-  if (!box_may_contribute(A, B, C, thr, gx - 15.f, gx, gy - 15.f, gy)) return 0u;
-  uint32_t mask = 0;
-#pragma unroll
-  for (int b = 0; b < N_BLK; ++b) {
-    const float bx = (float)((b & 1) * BLK_W), by = (float)((b >> 1) * BLK_H);
-    if (box_may_contribute(A, B, C, thr, gx - bx - (BLK_W - 1), gx - bx, gy - by - (BLK_H - 1), gy - by))
-      mask |= 1u << b;
-  }
-  return mask;
-}
+// q(d) = A dx^2 + 2 B dx dy + C dy^2, d = Gaussian centre - pixel, power = -q/2. A box of pixels MAY hold a
+// pixel that passes `power >= thr_exact` when the minimum of q over the box is small enough; thr (REC_THR)
+// already sits 0.02 below the exact threshold and a further 1e-5 * (magnitude of the terms) absorbs the
+// rounding of both the box evaluation and the kernels' own power polynomial. Non positive-definite
+// conics and NaNs are never culled. Masks: bit = 2 * (y / 4) + x / 8, one per 8x4 pixel block of the tile.
 
 // ---------------------------------------------------------------------------------------------
 // The pair kernels' mask (blend_fwd2 / blend_bwd2: warp = 8x8 pixel block). Same conservative
@@ -84,9 +40,10 @@ __device__ __forceinline__ uint32_t tile_block_mask(const float4 q0, const float
 //     both of its 8x4 positions, so the scalar twins read the same bytes and only do a little
 //     needless work);
 //   * the rounding slack 1e-5 * mag is formed once from the tile box, which bounds every sub-box.
-// Which entries survive differs from tile_block_mask only where neither test is tight: both keep every
-// entry that can pass the exact per-pixel test, so images, n_contrib and gradients do not depend on
-// the choice (tests/test_blend_twins_gpu.py runs both).
+// The test is conservative (it keeps every entry that can pass the exact per-pixel test), so images,
+// n_contrib and gradients do not depend on how tight it is; the packed kernels and their one-pixel twins
+// use different granularities of it and must agree bit for bit in the forward
+// (tests/test_blend_twins_gpu.py).
 // ---------------------------------------------------------------------------------------------
 // bounding box of the tile's pixels that can still change (see live_box_publish): the masks' first test
 // runs against it instead of the whole tile, at no extra cost
@@ -152,7 +109,7 @@ __device__ __forceinline__ LiveBox live_box_merge(const uint4* slots) {
   return L;
 }
 
-// 8-bit mask in tile_block_mask's bit layout, each 8x8 block's decision written to both of its bits.
+// 8-bit mask, each 8x8 block's decision written to both of its 8x4 bits.
 __device__ __forceinline__ uint32_t tile_block_mask_pairs(const float4 q0, const float4 q1, float tile_px,
                                                           float tile_py, const LiveBox live) {
   const float A = q0.z, B = q0.w, C = q1.x, thr = q1.z;

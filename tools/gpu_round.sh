@@ -25,7 +25,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
     --log-file $OUT/${TAG}_launches.csv $SHORT > $OUT/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 ncu --set full --clock-control none --import-source on \
-    -k regex:"${NCU_REGEX:-blend_bwd|blend_fwd|onesweep|duplicate|geom_bwd|preprocess_fwd}" -s ${NCU_SKIP:-83} -c ${NCU_COUNT:-22} \
+    -k regex:"${NCU_REGEX:-blend_bwd|blend_fwd|onesweep|duplicate|geom_bwd|preprocess_fwd}" -s ${NCU_SKIP:-93} -c ${NCU_COUNT:-26} \
     -o $OUT/${TAG}_prof -f $SHORT > $OUT/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 fi
