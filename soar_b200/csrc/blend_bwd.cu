@@ -829,6 +829,7 @@ int launch_blend_bwd(const BlendBwdArgs& a_in, int grid_y, cudaStream_t stream) 
         return SOAR_E_CUDA;
       }
       launch_bwd_packed(a, grid, stream);
+      KernelScope::count_extra_launch();
       launch_bwd_one_pixel_drawn(a, (int)min(a.n_tiles, sparse_below / 4u), stream);
     }
   }

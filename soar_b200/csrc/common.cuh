@@ -31,6 +31,8 @@ class KernelScope {
  public:
   KernelScope(int id, cudaStream_t stream);
   ~KernelScope();
+  // a scope that holds more than one <<<>>> (the blend's two layouts) counts the extra launches here
+  static void count_extra_launch();
 
  private:
   int id_;
