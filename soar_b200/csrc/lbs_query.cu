@@ -288,7 +288,7 @@ __global__ void __launch_bounds__(1024) lbs_query_build_kernel(const float* __re
       for (int w = 1; w < 32; ++w) { L[a] = fminf(L[a], s_red[a][w]); H[a] = fmaxf(H[a], s_red[3 + a][w]); }
     }
     const float ex = H[0] - L[0], ey = H[1] - L[1], ez = H[2] - L[2];
-    // h ~ 1.2 x the vertex spacing a surface filling the bounding box's faces would have
+    // h ~ h_scale x the vertex spacing a surface filling the bounding box's faces would have
     float h = h_scale * sqrtf(2.f * (ex * ey + ey * ez + ez * ex) / (float)V);
     h = fmaxf(h, 1e-6f * fmaxf(fmaxf(ex, ey), fmaxf(ez, 1e-30f)));
     if (!(h > 0.f)) h = 1.f;  // all vertices coincide
@@ -819,10 +819,13 @@ int soar_lbs_query_build_grid(const float* cano_vertices, int32_t V, void* grid,
   }
   {
     KernelScope ks(K_LBS_QUERY_BUILD, stream);
-    const char* hs = getenv("SOAR_LQ_HSCALE");  // tuning knob (tools/lq_bench.py); default 1.2
-    const float h_scale = hs ? (float)atof(hs) : 1.2f;
+    // cell edge in units of the mean surface spacing; tuning knob (tools/lq_prof.py). Measured at 2M
+    // points on the 10,475-vertex template (r02zn): 0.8 -> 4.64 ms, 0.9 -> 5.08, 1.0 -> 4.94, 1.1 -> 5.06,
+    // 1.2 -> 5.49, 0.6 -> 5.04: the dense regions (face, hands) want cells well below the MEAN spacing.
+    const char* hs = getenv("SOAR_LQ_HSCALE");
+    const float h_scale = hs ? (float)atof(hs) : 0.8f;
     lbs_query_build_kernel<<<1, 1024, 0, stream>>>(cano_vertices, V, (unsigned char*)grid,
-                                                   h_scale > 0.f ? h_scale : 1.2f);
+                                                   h_scale > 0.f ? h_scale : 0.8f);
   }
   SOAR_LAUNCH_CHECK("lbs_query_build_kernel");
   return SOAR_OK;
