@@ -552,8 +552,12 @@ lbs_query_grid_kernel(const float* __restrict__ points, int N, const unsigned ch
 // end under a sentinel key and are served by the per-point kernel in tail mode.
 // Neighbouring queries also share most of their K weight rows: sorted by cell, those 220-byte rows
 // hit in L1 instead of costing 6.6 KB of L2 traffic per point.
-constexpr int LQC_WARPS = 16;
-constexpr int LQC_THREADS = LQC_WARPS * 32;
+// Warps per CTA (one CTA per SM, the vertex table fills most of its shared memory). Measured at 2M points
+// (r02zp): 12 warps (154 registers) 5.54 ms, 16 (126) 4.65 ms, 20 (96) 4.28 ms, 24 (80 registers, 56 B of
+// spill) 4.15 ms: the selection's FMNMX chains want more warps to hide behind than registers. 24 warps when
+// the per-warp lists still fit beside the vertex table, else 16.
+constexpr int LQC_WARPS_MAX = 24;
+constexpr int LQC_WARPS_MIN = 16;
 constexpr int LQC_K = 30;
 constexpr unsigned long long LQC_EMPTY = ((unsigned long long)0x7f7fffffu << 32) | 0xffffffffull;
 
@@ -628,13 +632,15 @@ __device__ __forceinline__ void lqc_walk_ring(const LqGridHeader& g, const uint3
 // overflows (duplicated vertices) is handed to the per-point kernel through the redo list.
 constexpr int LQC_CAP = 32;  // list entries per query
 
-__global__ void __launch_bounds__(LQC_THREADS, 1)
+template <int LQC_WARPS>
+__global__ void __launch_bounds__(LQC_WARPS * 32, 1)
 lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned char* __restrict__ blob,
                        const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_vals,
                        const float* __restrict__ lbs_weights, int J, const float* __restrict__ bones,
                        float* __restrict__ out_weights, float* __restrict__ out_mats,
                        uint32_t* __restrict__ redo_list, uint32_t* __restrict__ redo_count) {
   constexpr int K = LQC_K;
+  constexpr int LQC_THREADS = LQC_WARPS * 32;
   const LqGridHeader g = *reinterpret_cast<const LqGridHeader*>(blob);
   const int V = g.V;
   const float* const gx = reinterpret_cast<const float*>(blob + sizeof(LqGridHeader));
@@ -752,8 +758,8 @@ lbs_query_cells_kernel(const float* __restrict__ points, int N, const unsigned c
   }
 }
 
-static size_t lqc_smem_bytes(int V) {
-  return ((size_t)4 * V + LQ_MAX_J * 12 + LQC_WARPS * LQ_MAX_J) * 4 + (size_t)LQC_WARPS * LQC_CAP * 32 * 2;
+static size_t lqc_smem_bytes(int V, int warps) {
+  return ((size_t)4 * V + LQ_MAX_J * 12 + warps * LQ_MAX_J) * 4 + (size_t)warps * LQC_CAP * 32 * 2;
 }
 static size_t lq_smem_bytes(int V) {
   return ((size_t)3 * V + LQ_MAX_J * 12 + LQ_WARPS * 64 * 2 + LQ_WARPS * LQ_MAX_J) * 4;
@@ -885,7 +891,8 @@ int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* gri
   cudaStream_t stream = (cudaStream_t)stream_;
   // the batched kernel is specialised on the reference's K = 30 and keeps (vertex, index) as 16-byte
   // shared-memory entries; anything else takes the per-point walk
-  if (K != LQC_K || V > LQG_PERM_SMEM_MAX_V || lqc_smem_bytes(V) > 227 * 1024 || N < 32 * LQC_WARPS ||
+  const int warps = lqc_smem_bytes(V, LQC_WARPS_MAX) <= 227 * 1024 ? LQC_WARPS_MAX : LQC_WARPS_MIN;
+  if (K != LQC_K || V > LQG_PERM_SMEM_MAX_V || lqc_smem_bytes(V, warps) > 227 * 1024 || N < 32 * warps ||
       workspace == nullptr)
     return soar_lbs_query_weights_grid(points, N, grid, V, lbs_weights, J, K, bones, out_weights,
                                        out_mats, stream_);
@@ -925,14 +932,22 @@ int soar_lbs_query_weights_cells(const float* points, int32_t N, const void* gri
   uint32_t* const redo_count = keys[res ^ 1];
   SOAR_CUDA_TRY(cudaMemsetAsync(redo_count, 0, sizeof(uint32_t), stream));
   {
-    const size_t smem = lqc_smem_bytes(V);
-    SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem));
-    const int grid_dim = min(sms, ceil_div(ceil_div(N, 32), LQC_WARPS));
+    const size_t smem = lqc_smem_bytes(V, warps);
+    const int grid_dim = min(sms, ceil_div(ceil_div(N, 32), warps));
     KernelScope ks(K_LBS_QUERY, stream);
-    lbs_query_cells_kernel<<<grid_dim, LQC_THREADS, smem, stream>>>(
-        points, N, (const unsigned char*)grid, keys[res], vals[res], lbs_weights, J, bones, out_weights,
-        out_mats, redo_list, redo_count);
+    if (warps == LQC_WARPS_MAX) {
+      SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_cells_kernel<LQC_WARPS_MAX>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      lbs_query_cells_kernel<LQC_WARPS_MAX><<<grid_dim, LQC_WARPS_MAX * 32, smem, stream>>>(
+          points, N, (const unsigned char*)grid, keys[res], vals[res], lbs_weights, J, bones, out_weights,
+          out_mats, redo_list, redo_count);
+    } else {
+      SOAR_CUDA_TRY(cudaFuncSetAttribute(lbs_query_cells_kernel<LQC_WARPS_MIN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      lbs_query_cells_kernel<LQC_WARPS_MIN><<<grid_dim, LQC_WARPS_MIN * 32, smem, stream>>>(
+          points, N, (const unsigned char*)grid, keys[res], vals[res], lbs_weights, J, bones, out_weights,
+          out_mats, redo_list, redo_count);
+    }
   }
   SOAR_LAUNCH_CHECK("lbs_query_cells_kernel");
   {
