@@ -73,6 +73,26 @@ def test_no_cpu_fallback():
         skin_gaussians(torch.zeros(4, 3), torch.zeros(4, 4), torch.zeros(4, 55), torch.zeros(55, 4, 4))
 
 
+def test_rasterize_views_rejects_cpu_tensors_and_mixed_sizes():
+    """The batched multi-view node has no CPU path either, and checks its arguments before any launch."""
+    from soar_b200.views import rasterize_views, shard_views
+    s = _settings()
+    kw = dict(means3D=torch.zeros(4, 3), opacities=torch.ones(4, 1), shs=torch.zeros(4, 1, 3),
+              scales=torch.ones(4, 3), rotations=torch.ones(4, 4))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        rasterize_views([s, s], **kw)
+    with pytest.raises(RuntimeError, match="one image size"):
+        rasterize_views([s, s._replace(image_height=s.image_height + 16)], **kw)
+    with pytest.raises(RuntimeError, match="no views"):
+        rasterize_views([], **kw)
+    with pytest.raises(RuntimeError, match="num_views"):
+        rasterize_views([s, s], means2D=torch.zeros(3, 4, 3), **kw)
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        rasterize_views([s], means3D=kw["means3D"], opacities=kw["opacities"], scales=kw["scales"],
+                        rotations=kw["rotations"])
+    assert shard_views(32, 3, 8) == [3, 11, 19, 27]
+
+
 def test_product_never_imports_the_oracle():
     """The oracle is test infrastructure: nothing under the product packages may name it."""
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
