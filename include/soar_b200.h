@@ -13,7 +13,8 @@
  *   - the library keeps no global state besides a thread-local error string;
  *     every scratch buffer is caller-owned (the python shim allocates them with
  *     torch and keeps them in the autograd ctx, like the reference does through
- *     its resize_ callbacks, DGR/rasterize_points.cu:27-33).
+ *     its resize_ callbacks, DGR/rasterize_points.cu:27-33). The single
+ *     exception, soar_mask_to_index_static, says so at its declaration.
  *   - return 0 on success, negative SOAR_E_* on error; soar_last_error() gives
  *     the message (the shim re-raises it as RuntimeError like the reference's
  *     C++ exceptions, DGR/rasterize_points.cu:50-52).
@@ -342,6 +343,26 @@ size_t soar_mask_index_workspace_bytes(int32_t N);
 int soar_mask_to_index(const uint8_t* mask, int32_t N, int32_t invert, int32_t* index_out,
                        uint32_t* count_out, void* workspace, size_t workspace_bytes,
                        soar_stream_t stream);
+/* soar_mask_to_index for callers that are not allowed to allocate device memory. It has no
+ * counterpart in the reference (which builds these lists with torch boolean indexing and so always
+ * allocates); it exists for hosts that reach this library from a place where cudaMalloc is off
+ * limits: a plugin running inside another engine's memory pool with no allocator handed to it, a
+ * real-time or signal-safe section, or a process whose device memory was fully budgeted up front.
+ * Same inputs, outputs and results as soar_mask_to_index, but the per-CTA counts are kept in a
+ * fixed array inside the library image instead of a caller workspace, so:
+ *   - N is limited to SOAR_MASK_INDEX_STATIC_MAX_ROWS; more rows -> SOAR_E_WORKSPACE and a message
+ *     pointing at soar_mask_to_index. The array is 16 KB per GPU, held from library load to exit.
+ *   - the call itself makes no cudaMalloc / cudaFree / allocating library call (keep
+ *     soar_prof_enable off: profiling creates events). The first call on each device looks up the
+ *     array's device address (cudaGetSymbolAddress, with that device current); make that first
+ *     call outside of any stream capture.
+ *   - every call on a device uses the same array. Calls that follow each other on one stream are
+ *     fine (nothing is carried over, nothing needs clearing); two calls that can run on the GPU at
+ *     the same time (different streams, or different host threads on different streams) race on it
+ *     and give wrong lists — serialise them, or use soar_mask_to_index with separate workspaces. */
+#define SOAR_MASK_INDEX_STATIC_MAX_ROWS (1 << 24)
+int soar_mask_to_index_static(const uint8_t* mask, int32_t N, int32_t invert, int32_t* index_out,
+                              uint32_t* count_out, soar_stream_t stream);
 #define SOAR_ROWS_MAX_TENSORS 32
 typedef struct SoarRowTensor {
   float* data;               /* row-major [rows, width]; NULL source = zeros       */

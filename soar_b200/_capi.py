@@ -237,6 +237,10 @@ SIGNATURES = {
         c_int32,
         [c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "soar_mask_to_index_static": (
+        c_int32,
+        [c_void_p, c_int32, c_int32, c_void_p, c_void_p, c_void_p],
+    ),
     "soar_rows_gather": (
         c_int32,
         [POINTER(SoarRowTensor), POINTER(SoarRowTensor), c_int32, c_void_p, c_int32, ctypes.c_int64,

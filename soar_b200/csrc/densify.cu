@@ -21,6 +21,7 @@
 //   split_rows_kernel       the new centres / scales of densify_and_split
 // All of it is HBM-bound elementwise / gather work: no tensor cores.
 #include <math.h>
+#include <mutex>
 #include "common.cuh"
 
 namespace soar {
@@ -408,6 +409,83 @@ int soar_mask_to_index(const uint8_t* mask, int32_t N, int32_t invert, int32_t* 
     mask_scatter_kernel<<<blocks, MC_THREADS, 0, stream>>>(mask, N, invert, counts, index_out);
   }
   SOAR_LAUNCH_CHECK("mask_to_index kernels");
+  return SOAR_OK;
+}
+
+// ---- soar_mask_to_index for callers that must not allocate -----------------------------------------
+// The per-CTA counts live in this array, which is part of the library image: every GPU that loads
+// the library carries SOAR_MASK_INDEX_STATIC_MAX_ROWS / MC_TILE + 1 words (16 KB) of it until the
+// process exits. On the host the NAME `g_mask_static_counts` is only a handle for the runtime (its
+// value is not a device address and must never be handed to a kernel); the address a kernel can
+// use comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int MASK_STATIC_MAX_BLOCKS = SOAR_MASK_INDEX_STATIC_MAX_ROWS / MC_TILE;
+static_assert(SOAR_MASK_INDEX_STATIC_MAX_ROWS % MC_TILE == 0, "the limit is a whole number of CTA tiles");
+static __device__ __align__(256) uint32_t g_mask_static_counts[MASK_STATIC_MAX_BLOCKS + 1];
+
+constexpr int MASK_STATIC_MAX_DEVICES = 64;
+static uint32_t* g_mask_static_ptr[MASK_STATIC_MAX_DEVICES];  // per device ordinal, NULL = not asked yet
+static std::mutex g_mask_static_mutex;
+
+// Device address of this device's copy of the array (set-up on the first call per device).
+static int mask_static_counts(uint32_t** out) {
+  int dev = -1;
+  SOAR_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= MASK_STATIC_MAX_DEVICES) {
+    set_error("soar_mask_to_index_static: device ordinal %d outside 0..%d", dev, MASK_STATIC_MAX_DEVICES - 1);
+    return SOAR_E_INVALID;
+  }
+  std::lock_guard<std::mutex> lock(g_mask_static_mutex);
+  if (!g_mask_static_ptr[dev]) {
+    void* p = nullptr;
+    SOAR_CUDA_TRY(cudaGetSymbolAddress(&p, g_mask_static_counts));
+    if (!p) {
+      set_error("soar_mask_to_index_static: cudaGetSymbolAddress gave a NULL address on device %d", dev);
+      return SOAR_E_CUDA;
+    }
+    g_mask_static_ptr[dev] = static_cast<uint32_t*>(p);
+  }
+  *out = g_mask_static_ptr[dev];
+  return SOAR_OK;
+}
+
+// Same three launches as soar_mask_to_index; only the home of the per-CTA counts differs. Nothing in
+// the array has to start at zero: the count kernel stores (not adds) words 0..blocks-1, the scan
+// rewrites exactly those, the scatter reads exactly those — so whatever an earlier call (a longer
+// mask, say) left behind is never read.
+int soar_mask_to_index_static(const uint8_t* mask, int32_t N, int32_t invert, int32_t* index_out,
+                              uint32_t* count_out, soar_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (N < 0 || !count_out) { set_error("soar_mask_to_index_static: bad arguments"); return SOAR_E_INVALID; }
+  if (N > SOAR_MASK_INDEX_STATIC_MAX_ROWS) {
+    set_error("soar_mask_to_index_static: %d rows, the built-in scratch holds at most %d "
+              "(use soar_mask_to_index with a caller-owned workspace)", N, SOAR_MASK_INDEX_STATIC_MAX_ROWS);
+    return SOAR_E_WORKSPACE;
+  }
+  if (N == 0) {
+    SOAR_CUDA_TRY(cudaMemsetAsync(count_out, 0, sizeof(uint32_t), stream));
+    return SOAR_OK;
+  }
+  if (!mask || !index_out) {
+    set_error("soar_mask_to_index_static: NULL mask or index_out");
+    return SOAR_E_INVALID;
+  }
+  uint32_t* counts = nullptr;
+  const int rc = mask_static_counts(&counts);
+  if (rc != SOAR_OK) return rc;
+  const int blocks = ceil_div(N, MC_TILE);
+  {
+    KernelScope ks(K_MASK_INDEX, stream);
+    mask_count_kernel<<<blocks, MC_THREADS, 0, stream>>>(mask, N, invert, counts);
+  }
+  {
+    KernelScope ks(K_MASK_INDEX, stream);
+    mask_scan_kernel<<<1, 1024, 0, stream>>>(counts, blocks, count_out);
+  }
+  {
+    KernelScope ks(K_MASK_INDEX, stream);
+    mask_scatter_kernel<<<blocks, MC_THREADS, 0, stream>>>(mask, N, invert, counts, index_out);
+  }
+  SOAR_LAUNCH_CHECK("mask_to_index_static kernels");
   return SOAR_OK;
 }
 
