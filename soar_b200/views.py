@@ -326,6 +326,11 @@ class _RasterizeViews(torch.autograd.Function):
             x.opacities, x.scales = _capi.ptr(opac_), _capi.ptr(scales_)
             x.rotations, x.cov3D_precomp = _capi.ptr(rot_), _capi.ptr(cov_)
             x.config_host_flags = _C._config_flags(s.config)
+            if x.config_host_flags & _capi.CFG_LRN_CAM:
+                # this node has no camera inputs to hand the gradient to; dropping it silently would
+                # train nothing. GaussianRasterizer (one view per call) returns camera gradients.
+                raise RuntimeError("rasterize_views: config[3] > 0 (learnable camera) is not supported by "
+                                   "the batched call; render such views through GaussianRasterizer")
 
         gb = (lib.soar_rast_geom_bytes(P) + 255) // 256 * 256
         ib = (lib.soar_rast_image_bytes(W, H) + 255) // 256 * 256
@@ -385,6 +390,9 @@ class _RasterizeViews(torch.autograd.Function):
         V, P, H, W = ctx.V, ctx.P, ctx.H, ctx.W
         none = (None,) * 10
         if ctx.state is None:
+            if P > 0 and getattr(ctx, "consumed", False):
+                raise RuntimeError("rasterize_views: backward called a second time; the per-view scratch "
+                                   "is released after the first backward (retain_graph is not supported)")
             return none
         views, keep, geom, img, binning, counts, radii, gb, ib, M, sh_ = ctx.state
         dev = geom.device
@@ -393,7 +401,10 @@ class _RasterizeViews(torch.autograd.Function):
         g_color, g_normal = f(g_color, "grad color"), f(g_normal, "grad normal")
         g_depth, g_opac = f(g_depth, "grad depth"), f(g_opac, "grad opac")
         sinks = ctx.sinks or {}
-        store_first = ctx.direct is not None and ctx.direct.first_store()
+        # only a node that owns sinks may use up the step's one store: a sink-less node (detached or
+        # derived inputs, e.g. an occupancy pass) running first would otherwise leave the owner adding
+        # into a flat buffer nobody has written yet (the per-view path guards the same way)
+        store_first = bool(sinks) and ctx.direct is not None and ctx.direct.first_store()
 
         def buf(name, shape):
             t = sinks.get(name)
@@ -459,6 +470,7 @@ class _RasterizeViews(torch.autograd.Function):
                     ctypes.c_void_p(per_view[v].cuda_stream)), "rasterize_views (backward)")
             _join(main, per_view)
         ctx.state = None
+        ctx.consumed = True
         n = ctx.needs
         return (None if k0 or not n[0] else d_means3D,
                 d_means2D if ctx.has_means2D and n[1] else None,

@@ -315,6 +315,59 @@ def test_rasterize_views_under_direct_accumulation(n_streams):
         assert rel_err(flat.grad(k), 2 * ref[k].grad) <= 1e-3, k
 
 
+def test_sinkless_node_does_not_use_up_the_first_store():
+    """A batched node whose inputs are NOT registered leaves (detached copies, like an occupancy pass)
+    may run its backward before the node that owns the sinks. It must leave the step's one STORE to the
+    owner: the flat buffer starts as NaN here, so an owner that adds instead of storing shows at once."""
+    from soar_b200.views import rasterize_views
+    n = 2
+    scenes, cot = _views(10_000, 128, 96, n, sh_degree=1)
+    base = {k: scenes[0][k] for k in KEYS}
+    sts = [settings_of(s) for s in scenes]
+    stack = lambda key: torch.stack([cot[key]] * n)
+    cots = [stack("color"), stack("normal"), stack("depth"), stack("opac")]
+
+    def render(p):
+        return rasterize_views(sts, means3D=p["means3D"], opacities=p["opacities"], shs=p["shs"],
+                               scales=p["scales"], rotations=p["rotations"])
+
+    ref = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    torch.autograd.backward(list(render(ref)[:4]), cots)
+
+    got = {k: v.clone().requires_grad_(True) for k, v in base.items()}
+    side = {k: v.clone().requires_grad_(True) for k, v in base.items()}   # leaves, but not in the buffer
+    flat = FlatGrads(got)
+    flat.flat.fill_(float("nan"))
+    with flat.direct(overwrite=True):
+        owner = render(got)
+        loose = render(side)
+        torch.autograd.backward(list(loose[:4]), cots)     # the sink-less node goes first
+        torch.autograd.backward(list(owner[:4]), cots)
+    torch.cuda.synchronize()
+    for k in KEYS:
+        assert bool(torch.isfinite(flat.grad(k)).all()), k
+        assert rel_err(flat.grad(k), ref[k].grad) <= 1e-3, k
+        assert rel_err(side[k].grad, ref[k].grad) <= 1e-3, k
+
+
+def test_rasterize_views_refuses_learnable_camera_and_second_backward():
+    from soar_b200.views import rasterize_views
+    scenes, cot = _views(2_000, 64, 64, 2, sh_degree=0)
+    s = scenes[0]
+    sts = [settings_of(x) for x in scenes]
+    cam = sts[1]._replace(config=torch.tensor([1.0, 0.0, 0.0, 1.0], device="cuda"))
+    with pytest.raises(RuntimeError, match="learnable camera"):
+        rasterize_views([sts[0], cam], means3D=s["means3D"], opacities=s["opacities"], shs=s["shs"],
+                        scales=s["scales"], rotations=s["rotations"])
+    p = {k: s[k].clone().requires_grad_(True) for k in KEYS}
+    out = rasterize_views(sts, means3D=p["means3D"], opacities=p["opacities"], shs=p["shs"],
+                          scales=p["scales"], rotations=p["rotations"])
+    loss = sum(t.sum() for t in out[:4])
+    loss.backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="second time"):
+        loss.backward()
+
+
 def test_rasterize_views_argument_errors_and_empty_cloud():
     from soar_b200.views import rasterize_views
     scenes, _ = _views(1_000, 64, 64, 2, sh_degree=0)
