@@ -62,10 +62,12 @@ class KernelScope {
 __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
-// Number of sort bits above the 32 depth bits: the reference's getHigherMsb()
-// (DGR/cuda_rasterizer/rasterizer_impl.cu:35-48) restated as "smallest b with
-// n >> b == 0" — identical for every n >= 1.
-// bits of the largest tile id, n_tiles - 1 (at least 1): 4096 tiles sort over 12 bits, not 13
+// Number of tile-id bits the pair sort runs over: the bit length of the LARGEST tile id,
+// n_tiles - 1 (at least 1 bit). This deliberately differs from the reference's getHigherMsb(n_tiles)
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:35-48), which returns the bit length of n_tiles itself and
+// so spends one bit too many whenever n_tiles is a power of two (4096 tiles: 13 there, 12 here).
+// Ids stay below n_tiles in both sort directions (the descending flip is applied to the digit, not
+// the id), so the sorted order is the same; tests/test_host_logic.py pins 1, 2, 4096 and 4097.
 inline int tile_id_bits(uint32_t n_tiles) {
   const uint32_t top = n_tiles > 1 ? n_tiles - 1 : 1;
   int b = 0;

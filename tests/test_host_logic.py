@@ -180,3 +180,27 @@ def test_bench_loss_helper_matches_autograd():
     assert torch.allclose(loss, ref.detach(), rtol=1e-6, atol=0)
     for c, g in zip(cots, grads):
         assert torch.allclose(c, g, rtol=1e-6, atol=1e-9)
+
+
+def test_tile_id_bits_is_the_bit_length_of_the_largest_id(tmp_path):
+    """common.cuh's tile_id_bits(): bits of n_tiles - 1, not the reference's getHigherMsb(n_tiles)
+    (DGR/cuda_rasterizer/rasterizer_impl.cu:35-48) — one bit fewer at powers of two. Built as a
+    host-only program with nvcc (no device needed)."""
+    import shutil
+    import subprocess
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "bits.cu"
+    src.write_text('#include "%s/soar_b200/csrc/common.cuh"\n'
+                   'namespace soar { void set_error(const char*, ...) {} }\n'
+                   'int main() { const unsigned n[] = {1u, 2u, 3u, 4096u, 4097u, 8160u, 16384u};\n'
+                   '  for (unsigned v : n) printf("%%u:%%d ", v, soar::tile_id_bits(v)); return 0; }\n' % root)
+    exe = tmp_path / "bits"
+    subprocess.run([nvcc, "-std=c++17", "-o", str(exe), str(src)], check=True, capture_output=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    got = dict((int(a), int(b)) for a, b in (x.split(":") for x in out))
+    assert got == {1: 1, 2: 1, 3: 2, 4096: 12, 4097: 13, 8160: 13, 16384: 14}
+    for n, b in got.items():
+        assert (n - 1) < (1 << b) and (n <= 2 or (n - 1) >= (1 << (b - 1)))
