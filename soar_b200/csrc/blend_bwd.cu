@@ -830,7 +830,7 @@ int launch_blend_bwd(const BlendBwdArgs& a_in, int grid_y, cudaStream_t stream) 
       }
       launch_bwd_packed(a, grid, stream);
       KernelScope::count_extra_launch();
-      launch_bwd_one_pixel_drawn(a, (int)min(a.n_tiles, sparse_below / 4u), stream);
+      launch_bwd_one_pixel_drawn(a, (int)max(1u, min(a.n_tiles, sparse_below / 4u)), stream);
     }
   }
   SOAR_LAUNCH_CHECK("blend_bwd_kernel");

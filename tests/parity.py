@@ -17,6 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REPORT = os.path.join(ROOT, "gpurun_out", "parity_report.jsonl")
 IMG_TOL = 1e-4
 GRAD_TOL = 1e-3
+GRAD_TOL_CAP = 5e-3   # the noise allowance never loosens the bar beyond this
 SIGNIFICANT = 1e-3   # per-element statistics run over elements with |ref| > SIGNIFICANT * max|ref|
 
 
@@ -46,9 +47,12 @@ def debug_tensors(s):
     _capi.check(lib.soar_rast_debug_sorted_keys(P, W, H, R, geom.data_ptr(), binning.data_ptr(),
                                                 keys.data_ptr() if R else None, None), "debug keys")
     torch.cuda.synchronize()
+    # slot T behind the ranges: .x = the frame's non-empty tile count (tile_ranges_kernel), which the
+    # blend launches above 2^20 pairs use to pick their layout on the device (kernels.h)
+    tail = grab(2, 2 * (T + 1), torch.int32).view(T + 1, 2)
     return dict(R=R, keys=keys, point_list=grab(1, R, torch.int32),
-                ranges=grab(2, 2 * T, torch.int32).view(T, 2), n_contrib=grab(3, H * W, torch.int32),
-                radii=radii)
+                ranges=tail[:T], nonempty_tiles=int(tail[T, 0].item()) if R else 0,
+                n_contrib=grab(3, H * W, torch.int32), radii=radii)
 
 
 def run_product(s, cot):
@@ -131,8 +135,9 @@ def _log(rec):
 
 def compare_grads(name, ours, ref, ref_again, pairs, tag=None):
     """Tensor-level bar (north_star): max|a-b| / max|b| <= max(1e-3, 10 x the reference's own
-    run-to-run figure). Per-element bar: the 99th-percentile relative error over significant
-    elements <= max(1e-3, 10 x the reference's own). Everything is printed and logged."""
+    run-to-run figure), capped at 5e-3. Per-element bar: the 99th-percentile relative error over
+    significant elements <= max(1e-3, 10 x the reference's own), same cap. Everything is printed and
+    logged."""
     rows, failures = {}, []
     for k in pairs:
         a, b, b2 = ours[k].reshape(-1), ref[k].reshape(-1), ref_again[k].reshape(-1)
@@ -140,9 +145,9 @@ def compare_grads(name, ours, ref, ref_again, pairs, tag=None):
         err, noise = rel_err(a, b), rel_err(b2, b)
         st, st_noise = element_stats(a, b), element_stats(b2, b)
         rows[k] = dict(err=err, noise=noise, elem=st, elem_noise=st_noise)
-        if err > max(GRAD_TOL, 10 * noise):
+        if err > min(max(GRAD_TOL, 10 * noise), GRAD_TOL_CAP):
             failures.append(f"dL/d{k}: tensor-relative {err:.3e} (reference self-noise {noise:.2e})")
-        if st["p99"] > max(GRAD_TOL, 10 * st_noise["p99"]):
+        if st["p99"] > min(max(GRAD_TOL, 10 * st_noise["p99"]), GRAD_TOL_CAP):
             failures.append(f"dL/d{k}: per-element p99 {st['p99']:.3e} (reference self-noise p99 {st_noise['p99']:.2e})")
     line = " | ".join(f"{k}: {r['err']:.1e} (noise {r['noise']:.1e}; elem med {r['elem']['med']:.1e} "
                       f"p99 {r['elem']['p99']:.1e} max {r['elem']['max']:.1e}, noise p99 {r['elem_noise']['p99']:.1e})"

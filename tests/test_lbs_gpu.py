@@ -212,3 +212,37 @@ def test_cell_batched_query_is_bit_identical_to_per_point_walk_at_2m():
     q.per_point = False
     m_fast = q.mats(pts, bones)
     assert ((m_fast == m_slow) | (m_fast.isnan() & m_slow.isnan())).all()
+
+
+def test_cell_batched_query_tie_overflow_goes_through_the_redo_list():
+    """40 coincident template vertices: every query whose K nearest include that spot has 40 candidates
+    at one and the same distance, more than the cell-batched kernel's per-lane list holds (32), so it
+    must hand those queries to the per-point kernel through its redo list (lbs_query.cu, `overflow`).
+    N is far above 32 x 24, so the cell-batched kernel is the one that runs. Bit-identical to the
+    per-point walk, weights and fused transforms, and the overflow condition is shown to occur."""
+    from soar_b200.lbs import SkinWeightQuery
+    m = synthetic.smplx_template(NB=1, seed=0)
+    verts = m["v_template"].clone()
+    spot = verts[100].clone()
+    verts[100:140] = spot                                   # 40 coincident vertices
+    N = 200_000
+    pts = synthetic.avatar_gaussians(N, m["v_template"], seed=1)["points"].cuda()
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    pts[:4000] = spot.cuda() + 0.01 * torch.randn(4000, 3, device="cuda", generator=gen)
+    # the condition itself, by brute force on a few of those queries: more than 32 vertices at or
+    # below the 30th smallest distance
+    d = ((pts[:64, None, :] - verts.cuda()[None, :, :]) ** 2).sum(-1)
+    kth = d.kthvalue(30, dim=1).values
+    assert ((d <= kth[:, None]).sum(1) > 32).any(), "the scene does not overflow the tie list"
+    q = SkinWeightQuery(verts.cuda(), m["lbs_weights"].cuda(), K=30)
+    fast = q(pts)
+    bones = synthetic.skinning_problem(8, seed=3)["bones"].cuda()
+    m_fast = q.mats(pts, bones)
+    q.per_point = True
+    slow = q(pts)
+    m_slow = q.mats(pts, bones)
+    assert torch.isfinite(fast).all()
+    assert torch.equal(fast, slow), f"{(fast != slow).any(1).sum().item()} of {N} points differ"
+    assert torch.equal(m_fast, m_slow)
+    # and the weights are a convex blend (rows sum to 1 like the template's)
+    assert (fast.sum(1) - 1).abs().max().item() < 1e-4

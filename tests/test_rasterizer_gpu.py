@@ -102,6 +102,31 @@ def test_forward_backward_matches_reference(case):
         assert (out["radii"] > 0).sum().item() < (run_ours(full)[0]["radii"] > 0).sum().item()
 
 
+def test_device_side_layout_choice_takes_both_branches():
+    """Blend launches above 2^20 pairs choose their layout on the device from the frame's non-empty
+    tile count (blend_fwd.cu / blend_bwd.cu launchers, threshold 16 x SMs). The comparisons with the
+    reference only cover BOTH layouts if some scene lands on each side with no environment override:
+    c3 (dense, 4096 tiles; compared in test_forward_backward_matches_reference) must be a
+    packed-layout frame; 400k Gaussians at 512^2 (1024 tiles) is a one-pixel-layout frame above the
+    small-launch cut and is compared with the reference here."""
+    import os
+    _need_ref()
+    for var in ("SOAR_BLEND_FWD_SCALAR", "SOAR_BLEND_BWD_SCALAR", "SOAR_BLEND_SPARSE_TILES"):
+        assert var not in os.environ, f"{var} is set: the parity cases would not exercise the device-side choice"
+    threshold = torch.cuda.get_device_properties(0).multi_processor_count * 16
+    seen = {}
+    for name, P, W, H, deg, seed in (("c3", 500_000, 1024, 1024, 3, 0), ("drawn_512_400k", 400_000, 512, 512, 1, 3)):
+        s = to_device(synthetic.scene(P, W, H, sh_degree=deg, seed=seed))
+        d = debug_tensors(s)
+        rng = d["ranges"].long()
+        assert d["nonempty_tiles"] == int((rng[:, 1] > rng[:, 0]).sum().item()), name
+        assert d["R"] > (1 << 20), (name, d["R"])
+        seen[name] = d["nonempty_tiles"]
+    assert seen["c3"] > threshold, seen                    # packed kernels run, drawn one-pixel CTAs exit
+    assert 0 < seen["drawn_512_400k"] <= threshold, seen   # the reverse
+    compare_with_reference("drawn_512_400k", s, to_device(synthetic.cotangents(512, 512, seed=3)))
+
+
 def test_cov3D_precomp_through_the_python_facade():
     """GaussianRasterizer(cov3D_precomp=..., scales=None, rotations=None) — the call the reference's
     facade allows but its kernel cannot survive (Q19). Here it renders with R = identity: bit-identical
