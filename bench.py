@@ -632,13 +632,28 @@ def timed(fn, arm, wl, steps, warmup, world, device):
     wl.flush_loss()
     barrier(world)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]   # one record per step, no sync
     e0.record()
     for s in range(steps):
         fn(arm, wl, warmup + s)
+        marks[s].record()
     wl.flush_loss()   # e2e: the last step's loss is read before the clock stops (no-op otherwise)
     e1.record()
     barrier(world)
+    # spread over the steps of this rank (SURVEY 8(d) protocol): device time between consecutive marks
+    per = sorted(a.elapsed_time(b) for a, b in zip([e0] + marks[:-1], marks))
+    pick = lambda q: per[min(len(per) - 1, int(round(q * (len(per) - 1))))]
+    LAST_STEP_SPREAD.clear()
+    LAST_STEP_SPREAD.update({"p10_ms": round(pick(0.1), 4), "p50_ms": round(pick(0.5), 4),
+                             "p90_ms": round(pick(0.9), 4), "n": len(per), "rank": 0 if world == 1 else dist.get_rank()})
     return max_over_ranks(e0.elapsed_time(e1), world, device)
+
+
+LAST_STEP_SPREAD = {}   # filled by timed(): per-step device times of the run it just timed
+
+
+# smsp__inst_executed.sum per launch at c3 (one view), profiles/r02z_ncu_summary.txt
+C3_WARP_INSTRUCTIONS = {"blend_bwd": 275362997, "blend_fwd": 154142283}
 
 
 def scene_stats(wl, arm):
@@ -1306,6 +1321,7 @@ def main():
     n0 = lib.soar_launch_count() if soar else 0
     ms = timed(step_resident, arm, wl, args.steps, args.warmup, world, device)
     launches = int(lib.soar_launch_count() - n0) if soar else None
+    step_spread = dict(LAST_STEP_SPREAD)
     clk = clocks.stop() if rank == 0 else None
     frames = args.steps * wl.views_per_step
     value = frames / (ms / 1e3)
@@ -1325,7 +1341,7 @@ def main():
     e2e = None
     if not args.no_e2e:
         ms_e = timed(step_e2e, arm, wl, args.steps, max(3, args.warmup // 2), world, device)
-        e2e = {"value": frames / (ms_e / 1e3), "unit": "frames/s",
+        e2e = {"value": frames / (ms_e / 1e3), "unit": "frames/s", "step_spread": dict(LAST_STEP_SPREAD),
                "h2d_bytes_per_step": wl.h2d_bytes_per_step(), "d2h_bytes_per_step": 4,
                "ms_per_step": ms_e / args.steps,
                "targets": "float32" if args.float_targets else
@@ -1372,8 +1388,21 @@ def main():
                 traffic = td.get("bytes_per_launch", {}).get(top)
                 traffic_src = os.path.basename(tj[-1])
         b_top, per_frame_top = alg.get(top, (0, 1))
+        # The dominant kernels are issue-bound, so the HBM fraction is low by construction:
+        # print the bound that binds as well. Warp instructions per launch come from the committed ncu
+        # capture (smsp__inst_executed.sum, one c3 view) — not measured in this run, and labelled so.
+        issue = None
+        if args.workload == "c3" and top in C3_WARP_INSTRUCTIONS:
+            sms = torch.cuda.get_device_properties(device).multi_processor_count
+            mhz = (clk or {}).get("sm_mhz") or 1965.0
+            floor_ms = C3_WARP_INSTRUCTIONS[top] / (sms * 4 * mhz * 1e6) * 1e3   # 4 schedulers/SM, 1 warp-instr/clk each
+            issue = {"warp_instructions_per_launch": C3_WARP_INSTRUCTIONS[top], "live": False,
+                     "source": "profiles/r02z_ncu_summary.txt (smsp__inst_executed.sum)",
+                     "sm_mhz": mhz, "floor_ms": floor_ms, "frac": floor_ms / (t / cnt)}
         roofline = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                     "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "traffic_live": False if traffic is not None else None,
+                    "issue_frac": issue["frac"] if issue else None, "issue": issue,
                     "algorithmic_bytes": b_top / per_frame_top, "avg_ms": t / cnt, "launches": cnt,
                     "peak_source": peak_src}
         shares = {k: {"launches": c, "ms": round(tt, 4), "share": round(tt / tot, 4),
@@ -1415,7 +1444,7 @@ def main():
                           + (f"; views spread over {len(wl.streams)} CUDA streams, additions in view order"
                              if wl.streams else ""))
             if (wl.pipelined and soar) else "one blocking forward+backward per view, gradients accumulated with add_",
-            "clocks": clk, "e2e": e2e, "sequential": sequential, "gpu_launches": launches,
+            "step_spread": step_spread, "clocks": clk, "e2e": e2e, "sequential": sequential, "gpu_launches": launches,
             "allreduce": verified, "allreduce_ms": ar_ms,
             "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
             "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "gpu_baselines": gpub, "lbs": lbs,

@@ -246,3 +246,95 @@ def test_cell_batched_query_tie_overflow_goes_through_the_redo_list():
     assert torch.equal(m_fast, m_slow)
     # and the weights are a convex blend (rows sum to 1 like the template's)
     assert (fast.sum(1) - 1).abs().max().item() < 1e-4
+
+
+def _m2q_candidates(M):
+    """The four candidate quaternions of pytorch3d's matrix_to_quaternion for M [N,3,3] (float64) and
+    their q_abs, written out candidate by candidate (w-, x-, y-, z-dominant)."""
+    m = M.double()
+    m00, m01, m02 = m[:, 0, 0], m[:, 0, 1], m[:, 0, 2]
+    m10, m11, m12 = m[:, 1, 0], m[:, 1, 1], m[:, 1, 2]
+    m20, m21, m22 = m[:, 2, 0], m[:, 2, 1], m[:, 2, 2]
+    q2 = torch.stack([1 + m00 + m11 + m22, 1 + m00 - m11 - m22, 1 - m00 + m11 - m22, 1 - m00 - m11 + m22], 1)
+    q_abs = q2.clamp(min=0).sqrt()
+    num = torch.stack([
+        torch.stack([q2[:, 0].clamp(min=0), m21 - m12, m02 - m20, m10 - m01], 1),
+        torch.stack([m21 - m12, q2[:, 1].clamp(min=0), m10 + m01, m02 + m20], 1),
+        torch.stack([m02 - m20, m10 + m01, q2[:, 2].clamp(min=0), m12 + m21], 1),
+        torch.stack([m10 - m01, m20 + m02, m21 + m12, q2[:, 3].clamp(min=0)], 1)], 1)       # [N,4 cand,4]
+    cand = num / (2 * q_abs.clamp(min=0.1))[:, :, None]
+    cand = torch.where(cand[:, :, 0:1] < 0, -cand, cand)                                    # standardize
+    return torch.nn.functional.normalize(cand, dim=-1), q_abs
+
+
+def _skin_identity_quats(mats3):
+    """Runs the product's skinning with one bone per point (one-hot weights) and identity input
+    quaternions, so the matrix handed to its matrix_to_quaternion is exactly mats3[n]."""
+    from soar_b200.lbs import skin_gaussians
+    out = []
+    for lo in range(0, mats3.shape[0], 48):
+        blk = mats3[lo:lo + 48]
+        n = blk.shape[0]
+        bones = torch.zeros(n, 4, 4)
+        bones[:, :3, :3] = blk
+        bones[:, 3, 3] = 1
+        quats = torch.tensor([1.0, 0, 0, 0]).repeat(n, 1)
+        _, q, _ = skin_gaussians(torch.zeros(n, 3).cuda(), quats.cuda(), torch.eye(n).cuda(), bones.cuda())
+        out.append(q.cpu())
+    return torch.cat(out)
+
+
+def test_matrix_to_quaternion_branch_choice_on_non_orthonormal_matrices():
+    """a19's unpinned half (pytorch3d is not vendored by the reference and absent here): the branch
+    choice, which is what matters once bone blends stop being rotations. For sheared /
+    scaled matrices the four candidates are four DIFFERENT quaternions, so which one the kernel
+    returned can be read off its output: it must be the candidate with the largest q_abs, the FIRST
+    of them on an exact tie (torch.argmax). The 0.1 floor never binds on the selected candidate
+    (the four q_abs^2 sum to 4, so the largest is >= 1); it is asserted rather than assumed."""
+    gen = torch.Generator().manual_seed(11)
+    # rotations whose dominant quaternion component is w, x, y, z in turn, then sheared and scaled
+    q = torch.nn.functional.normalize(0.35 * torch.randn(4, 200, 4, generator=gen), dim=-1)
+    for c in range(4):
+        q[c, :, c] = q[c, :, c].abs() + 1.5
+    q = torch.nn.functional.normalize(q.reshape(-1, 4), dim=-1)
+    R = lbs_oracle.quaternion_to_matrix(q)
+    A = torch.eye(3) + 0.25 * torch.randn(q.shape[0], 3, 3, generator=gen)
+    mats = torch.matmul(A, R)
+    # exact ties between the x and y candidates (m00 == m11) and between w and z (m00 == -m11), with
+    # off-diagonal entries that make the tied candidates differ
+    ties = torch.tensor([[[0.0, 1.0, 0.0], [1.0, 0.0, 0.0], [0.0, 0.3, -1.0]],
+                         [[0.5, 0.9, 0.1], [0.7, 0.5, 0.0], [0.2, 0.4, -1.0]],
+                         [[0.25, -0.8, 0.2], [0.6, -0.25, 0.1], [0.0, 0.3, 0.5]]])
+    mats = torch.cat([mats, ties])
+    got = _skin_identity_quats(mats).double()
+    cand, q_abs = _m2q_candidates(mats)
+    want_sel = q_abs.argmax(1)                                # first maximal index on ties
+    assert (q_abs.gather(1, want_sel[:, None]) >= 1.0 - 1e-12).all()
+    for c in range(4):
+        assert (want_sel[:800] == c).sum() >= 100, "the cases do not reach every branch"
+    assert q_abs[800, 1] == q_abs[800, 2] and q_abs[801, 1] == q_abs[801, 2] and q_abs[802, 0] == q_abs[802, 3]
+    err = (cand - got[:, None, :]).abs().amax(-1)             # [N,4]: distance to each candidate
+    chosen = err.gather(1, want_sel[:, None])[:, 0]
+    assert chosen.max().item() <= 2e-5, f"selected candidate off by {chosen.max().item():.2e}"
+    # the identification is unambiguous wherever another candidate is far from the selected one
+    other = err.clone()
+    other.scatter_(1, want_sel[:, None], float("inf"))
+    distinct = (cand - cand.gather(1, want_sel[:, None, None].expand(-1, 1, 4))).abs().amax(-1)
+    distinct.scatter_(1, want_sel[:, None], float("inf"))
+    clear = distinct.amin(1) > 1e-3
+    assert clear[800:].all() and clear[:800].float().mean().item() > 0.9
+    assert (other.amin(1)[clear] > 5e-4).all(), "the output matches a candidate other than the arg-max one"
+
+
+def test_matrix_to_quaternion_against_pytorch3d_when_present():
+    """Opportunistic pin: where a real pytorch3d is importable, the kernel's quaternions are compared
+    with pytorch3d.transforms.matrix_to_quaternion itself on non-orthonormal bone blends. Skipped (and
+    a19 stays 'parity unpinned') wherever pytorch3d is absent — it is in this image."""
+    p3d = pytest.importorskip("pytorch3d.transforms")
+    pb = synthetic.skinning_problem(50_000, seed=9)
+    blended = torch.einsum("nj,jxy->nxy", pb["weights"], pb["bones"].reshape(-1, 4, 4))[:, :3, :3]
+    sel = torch.arange(0, 50_000, 50)
+    got = _skin_identity_quats(blended[sel])
+    want = torch.nn.functional.normalize(p3d.matrix_to_quaternion(blended[sel]), dim=-1)
+    want = torch.where(want[:, 0:1] < 0, -want, want)
+    assert (got - want).abs().max().item() <= 2e-5
