@@ -1447,6 +1447,7 @@ def main():
             "step_spread": step_spread, "clocks": clk, "e2e": e2e, "sequential": sequential, "gpu_launches": launches,
             "allreduce": verified, "allreduce_ms": ar_ms,
             "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
+            "allreduce_buffer": getattr(wl.flat, "buffer_kind", None) if soar else None,
             "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "gpu_baselines": gpub, "lbs": lbs,
             "postops": post, "c5_step": c5, "densify": dens,
         }

@@ -124,6 +124,66 @@ def direct_sink(t):
     return hit[1]
 
 
+_NCCL_POOLS = []   # (backend, pool) of every registered flat buffer, dropped before the group goes away
+
+
+def release_registered_buffers():
+    """Deregisters the NCCL-registered flat buffers from their communicator. Must run before
+    `dist.destroy_process_group()` (the pool's destructor would otherwise reach for an aborted
+    communicator at interpreter exit); FlatGrads installs a wrapper around destroy_process_group
+    that does it, so callers only need this when they tear NCCL down some other way."""
+    while _NCCL_POOLS:
+        backend, pool = _NCCL_POOLS.pop()
+        try:
+            backend.deregister_mem_pool(pool)
+        except Exception:  # noqa: BLE001  (already gone with its communicator)
+            pass
+
+
+def _wrap_destroy_once():
+    if getattr(dist.destroy_process_group, "_soar_wrapped", False):
+        return
+    inner = dist.destroy_process_group
+
+    def destroy_process_group(*a, **kw):
+        release_registered_buffers()
+        return inner(*a, **kw)
+
+    destroy_process_group._soar_wrapped = True
+    dist.destroy_process_group = destroy_process_group
+
+
+def _nccl_registered_zeros(n, dev):
+    """The flat gradient buffer -> (tensor, pool or None, description). Under an NCCL process group of
+    more than one rank it is carved from NCCL's own allocator (ncclMemAlloc) and registered with the
+    communicator once as a symmetric window, so the per-step all-reduce runs on a user-registered
+    buffer instead of staging through NCCL's internal ones: 118 MB over 8 B200s 0.378 -> 0.277 ms
+    (profiles/r03c_*). SOAR_FLAT_NCCL_POOL=0 keeps a plain torch allocation, =1 registers without the
+    symmetric window (0.341 ms). Any failure of the (version-dependent) torch hooks falls back to
+    the plain allocation with a warning: this is an allocation strategy, not a compute path."""
+    import os
+    import warnings
+    mode = os.environ.get("SOAR_FLAT_NCCL_POOL", "2")
+    plain = lambda: torch.zeros(n, dtype=torch.float32, device=dev)
+    if (mode == "0" or dev.type != "cuda" or not (dist.is_available() and dist.is_initialized())
+            or dist.get_world_size() == 1 or dist.get_backend() != "nccl"):
+        return plain(), None, "plain torch allocation"
+    try:
+        backend = dist.group.WORLD._get_backend(torch.device(dev))
+        pool = torch.cuda.MemPool(backend.mem_allocator)
+        with torch.cuda.use_mem_pool(pool, device=dev):
+            flat = torch.zeros(n, dtype=torch.float32, device=dev)
+        backend.register_mem_pool(pool, symm=(mode != "1"))
+        _NCCL_POOLS.append((backend, pool))
+        _wrap_destroy_once()
+        return flat, pool, ("ncclMemAlloc pool registered with the communicator"
+                            + (" as a symmetric window" if mode != "1" else ""))
+    except Exception as e:  # noqa: BLE001
+        warnings.warn(f"FlatGrads: NCCL-registered allocation unavailable ({type(e).__name__}: {e}); "
+                      "using a plain allocation")
+        return plain(), None, "plain torch allocation (registration failed)"
+
+
 class FlatGrads:
     """One contiguous fp32 buffer holding the gradients of all Gaussian parameters.
 
@@ -143,7 +203,7 @@ class FlatGrads:
         for k, n in zip(self.names, sizes):
             self.slices[k] = (off, off + n)
             off += (n + 3) // 4 * 4
-        self.flat = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.flat, self.nccl_pool, self.buffer_kind = _nccl_registered_zeros(off, dev)
         self._events = []   # pool for _Direct.order_events
         self.attach()
 
