@@ -158,16 +158,23 @@ def _nccl_registered_zeros(n, dev):
     more than one rank it is carved from NCCL's own allocator (ncclMemAlloc) and registered with the
     communicator once as a symmetric window, so the per-step all-reduce runs on a user-registered
     buffer instead of staging through NCCL's internal ones: 118 MB over 8 B200s 0.378 -> 0.277 ms
-    (profiles/r03c_*). SOAR_FLAT_NCCL_POOL=0 keeps a plain torch allocation, =1 registers without the
-    symmetric window (0.341 ms). Any failure of the (version-dependent) torch hooks falls back to
+    (profiles/r03c_*); with fewer than 4 ranks the plain allocation is faster and is kept.
+    SOAR_FLAT_NCCL_POOL=0 forces a plain torch allocation, =1 registration without the symmetric
+    window (0.341 ms at 8 ranks), =2 the window. Any failure of the (version-dependent) torch hooks falls back to
     the plain allocation with a warning: this is an allocation strategy, not a compute path."""
     import os
     import warnings
-    mode = os.environ.get("SOAR_FLAT_NCCL_POOL", "2")
+    mode = os.environ.get("SOAR_FLAT_NCCL_POOL", "auto")
     plain = lambda: torch.zeros(n, dtype=torch.float32, device=dev)
     if (mode == "0" or dev.type != "cuda" or not (dist.is_available() and dist.is_initialized())
             or dist.get_world_size() == 1 or dist.get_backend() != "nccl"):
         return plain(), None, "plain torch allocation"
+    if mode == "auto":
+        # measured on B200 / NVSwitch, 118 MB (profiles/r03c..e): plain / symmetric = 0.265 / 0.322 ms at
+        # 2 ranks, 0.324 / 0.298 at 4, 0.378 / 0.277 at 8 — the window pays from 4 ranks on
+        if dist.get_world_size() < 4:
+            return plain(), None, "plain torch allocation (fewer than 4 ranks)"
+        mode = "2"
     try:
         backend = dist.group.WORLD._get_backend(torch.device(dev))
         pool = torch.cuda.MemPool(backend.mem_allocator)
