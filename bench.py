@@ -1064,6 +1064,47 @@ def gpu_baselines(device):
     return out
 
 
+def verify_replica_densify(world, rank, device, N=60_000):
+    """view-sharded replicas must stay identical through the optimiser and a densify cycle.
+    Every rank starts from the same parameters, sees DIFFERENT views (its own gradients, radii and
+    screen-space gradients), all-reduces the parameter gradients, steps Adam, and after the third
+    step runs one densify + prune cycle on all-reduced statistics with identically seeded split
+    samples (GaussianStore.densify_cycle). Then P and a checksum over the raw bits of every
+    parameter, Adam moment and statistic are compared across ranks (MIN == MAX)."""
+    from soar_b200 import synthetic
+    from soar_b200.densify import GROUPS, GaussianStore
+    pb = synthetic.densify_problem(N, R=3, seed=0, n_adam=0, n_views=0)
+    st = GaussianStore(*(pb["params"][k].to(device) for k in GROUPS))
+    st.training_setup(pb["lrs"])
+    mine = synthetic.densify_problem(N, R=3, seed=1000 + rank, n_adam=3, n_views=3)   # this rank's views
+    P0 = st.num_points
+    for i in range(3):
+        g = {k: v.to(device) for k, v in mine["adam_grads"][i].items()}
+        vg, radii, sg = (t.to(device) for t in mine["views"][i])
+        st.add_densification_stats(vg, radii, sg)                  # local: this rank's view only
+        flat = torch.cat([g[k].reshape(-1) for k in GROUPS])
+        dist.all_reduce(flat)                                      # the step's gradient all-reduce
+        off = 0
+        for k in GROUPS:
+            n = g[k].numel()
+            g[k] = flat[off:off + n].view_as(g[k])
+            off += n
+        st.step(g)
+    n_clone, n_split, n_pruned = st.densify_cycle(max_grad=1.2, min_opacity=0.05, extent=2.0, seed=7)
+    cs = st.replica_checksum()
+    lo, hi = cs.clone(), cs.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    if int(hi[0].item()) <= P0 // 4 or min(n_clone, n_split, n_pruned) == 0:
+        raise RuntimeError(f"verify_replica_densify: degenerate cycle (P {P0} -> {int(hi[0].item())}, "
+                           f"{n_clone} cloned, {n_split} split, {n_pruned} pruned)")
+    return {"replicas_identical": bool(torch.equal(lo, hi)), "ranks": world, "P_before": P0,
+            "P_after": int(hi[0].item()), "cloned": n_clone, "split": n_split, "pruned": n_pruned,
+            "what": "3 Adam steps on all-reduced gradients + 1 prune + densify cycle on all-reduced statistics, "
+                    "seeded split samples; P and a bit-level checksum of parameters, moments and statistics "
+                    "compared over ranks"}
+
+
 def verify_allreduce(arm, wl, world, rank, device):
     """Outside the timed region, once: the all-reduced flat buffer must equal the sum of every rank's
     local (pre-collective) buffer, gathered to rank 0 and summed in float64 (<= 1e-5 relative)."""
@@ -1314,6 +1355,7 @@ def main():
         lib = _capi.load()
 
     verified = verify_allreduce(arm, wl, world, rank, device)
+    replica = verify_replica_densify(world, rank, device) if soar and world > 1 else None
 
     clocks = ClockSampler(local)
     if rank == 0:
@@ -1448,6 +1490,7 @@ def main():
             "allreduce": verified, "allreduce_ms": ar_ms,
             "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
             "allreduce_buffer": getattr(wl.flat, "buffer_kind", None) if soar else None,
+            "replica_densify": replica,
             "roofline": roofline, "kernels": shares, "cpu_baseline": cpu, "gpu_baselines": gpub, "lbs": lbs,
             "postops": post, "c5_step": c5, "densify": dens,
         }

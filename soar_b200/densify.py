@@ -21,6 +21,7 @@ import ctypes
 from typing import Dict, Optional
 
 import torch
+import torch.distributed as dist
 
 from . import _capi
 
@@ -38,6 +39,35 @@ def _stream():
 
 def _rows(t):
     return t.shape[0], (t.numel() // t.shape[0] if t.shape[0] else int(torch.tensor(t.shape[1:]).prod()))
+
+
+def allreduce_densify_stats(stats: Dict[str, torch.Tensor], group=None):
+    """Makes the densification statistics of view-sharded replicas identical: the five
+    accumulators and `denom` are SUMS over rendered views, so their all-reduce(SUM) over the ranks is
+    what one process rendering every view would hold; `max_radii2D` is a running maximum, so it takes
+    all-reduce(MAX). It has to be these statistics and not the raw screen-space gradient that is
+    reduced: the per-view quantity is a norm (TS/geometry/surfel_base.py:1113-1117), which is not linear.
+    Two collectives (one stacked SUM, one MAX) on whatever device the tensors live on; no-op without an
+    initialised process group or with a single rank. Summation order over ranks is NCCL's / gloo's and
+    the same on every rank, so all ranks end up with bit-identical statistics and hence take
+    bit-identical clone / split / prune decisions."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    sums = [k for k in STATS if k != "max_radii2D"]
+    packed = torch.stack([stats[k] for k in sums])
+    dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+    for i, k in enumerate(sums):
+        stats[k].copy_(packed[i])
+    dist.all_reduce(stats["max_radii2D"], op=dist.ReduceOp.MAX, group=group)
+
+
+def replica_generator(device, seed: int, cycle: int) -> torch.Generator:
+    """A generator every replica seeds identically for densify cycle number `cycle`: the split samples
+    (torch.normal, TS/geometry/surfel_base.py:1000) then come out the same on every rank (same GPU
+    model, same shapes, same seed), which keeps the replicas' parameters bit-identical after a split."""
+    g = torch.Generator(device=device)
+    g.manual_seed((int(seed) * 1_000_003 + int(cycle)) & 0x7FFFFFFFFFFFFFFF)
+    return g
 
 
 class GaussianStore:
@@ -265,7 +295,7 @@ class GaussianStore:
         self._append_selected(idx, n, 1)
         return n
 
-    def densify_and_split(self, selected_pts_mask, N=2, samples=None):
+    def densify_and_split(self, selected_pts_mask, N=2, samples=None, generator=None):
         """Replace every selected Gaussian by N samples of it (:979-1034): new centres
         R(q)·samples + xyz with samples ~ N(0, get_scaling), scales / (0.8 N), every other parameter
         repeated; the originals are pruned. `samples` [N·n_sel, 3] may be passed in (tests); by
@@ -277,7 +307,7 @@ class GaussianStore:
         n_new = n_sel * N
         if samples is None:
             stds = self.get_scaling[idx.long()].repeat(N, 1)
-            samples = torch.normal(mean=torch.zeros_like(stds), std=stds)
+            samples = torch.normal(mean=torch.zeros_like(stds), std=stds, generator=generator)
         samples = samples.detach().to(torch.float32).contiguous()
         new_xyz = torch.empty((n_new, 3), dtype=torch.float32, device=self.device)
         new_scaling = torch.empty((n_new, 3), dtype=torch.float32, device=self.device)
@@ -299,11 +329,42 @@ class GaussianStore:
         self.prune_points(mask)
         return mask
 
-    def adaptive_densify(self, max_grad, extent, N=2, samples=None):
+    def adaptive_densify(self, max_grad, extent, N=2, samples=None, generator=None):
         """:1083-1111 — clone the small high-gradient Gaussians, split the large ones. Both masks come
         from the statistics as they are BEFORE the clone resets them (the reference computes
         `grad_pos` first and passes it to both calls)."""
         clone_mask, split_mask = self._select(0, max_grad=max_grad, extent=extent)
         n_clone = self.densify_and_clone(clone_mask)
-        n_split = self.densify_and_split(split_mask, N=N, samples=samples)
+        n_split = self.densify_and_split(split_mask, N=N, samples=samples, generator=generator)
         return n_clone, n_split
+
+    # ---- view-sharded replicas (SURVEY 8(e)) -------------------------------------------------------
+    def sync_stats(self, group=None):
+        """All-reduce the statistics over the ranks (allreduce_densify_stats). Call it once, right
+        before adaptive_densify / adaptive_prune, on every rank."""
+        allreduce_densify_stats(self.stats, group)
+
+    def densify_cycle(self, max_grad, min_opacity, extent, N=2, seed=0, group=None):
+        """One replica-consistent prune + densify cycle: statistics all-reduced, split samples drawn
+        from a generator seeded with (seed, cycle number), so every rank mutates its replica the same
+        way and ends with the same P. Returns (n_clone, n_split, n_pruned). Rebuild anything sized by
+        P afterwards (FlatGrads(store.p) for the gradient buffer)."""
+        self.sync_stats(group)
+        self.cycles = getattr(self, "cycles", 0) + 1
+        gen = replica_generator(self.device, seed, self.cycles)
+        # prune first: the densify postfix zeroes the statistics (max_radii2D included), and a prune
+        # after it would see every Gaussian as never rendered
+        mask = self.adaptive_prune(min_opacity, extent)
+        n_clone, n_split = self.adaptive_densify(max_grad, extent, N=N, generator=gen)
+        return n_clone, n_split, int(mask.sum().item())
+
+    def replica_checksum(self):
+        """[P, sum of the raw bits of every parameter, moment and statistic] as int64 — equal across
+        ranks iff (up to hash collisions) the replicas are bit-identical."""
+        tot = torch.zeros((), dtype=torch.int64, device=self.device)
+        for i, (_, _, t) in enumerate(self._all_tensors()):
+            if t.numel():
+                bits = t.contiguous().view(torch.int32).to(torch.int64)
+                w = torch.arange(bits.numel(), device=self.device, dtype=torch.int64).view_as(bits) % 8191 + 1 + i
+                tot = tot + (bits * w).sum()
+        return torch.stack([torch.tensor(self.num_points, dtype=torch.int64, device=self.device), tot])

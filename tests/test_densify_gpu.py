@@ -146,3 +146,35 @@ def test_full_size_properties_2m():
     assert torch.allclose(kids, parents.repeat(2, 1) / 1.6, rtol=1e-5)
     assert (st.p["scaling"][-2 * ns:, 2] == -1e10).all()
     assert torch.isfinite(st.p["xyz"]).all()
+
+
+def test_densify_cycle_is_a_function_of_state_and_seed():
+    """What keeps view-sharded replicas identical: given the same parameters, moments
+    and (all-reduced) statistics, densify_cycle with the same seed ends in the same bits and the
+    same P; another seed draws other split samples. Single process: sync_stats is a no-op here, the
+    collective itself is covered on gloo (tests/test_host_logic.py) and at N=2 in bench.py."""
+    from soar_b200 import synthetic
+    from soar_b200.densify import GROUPS, GaussianStore
+    pb = synthetic.densify_problem(30_000, R=3, seed=4, n_adam=2, n_views=2)
+
+    def run(seed):
+        st = GaussianStore(*(pb["params"][k].cuda() for k in GROUPS))
+        st.training_setup(pb["lrs"])
+        for i in range(2):
+            vg, radii, sg = (t.cuda() for t in pb["views"][i])
+            st.add_densification_stats(vg, radii, sg)
+            st.step({k: v.cuda() for k, v in pb["adam_grads"][i].items()})
+        counts = st.densify_cycle(max_grad=1.2, min_opacity=0.05, extent=2.0, seed=seed)
+        return st, counts
+
+    a, ca = run(7)
+    b, cb = run(7)
+    c, cc = run(8)
+    assert ca == cb and min(ca) > 0, ca                       # clones, splits and prunes all happen
+    assert a.num_points == b.num_points == 30_000 - ca[2] + ca[0] + ca[1] * 2 - ca[1] and a.num_points > 10_000
+    assert torch.equal(a.replica_checksum(), b.replica_checksum())
+    for k in GROUPS:
+        assert torch.equal(a.p[k], b.p[k]) and torch.equal(a.exp_avg[k], b.exp_avg[k]), k
+    assert cc[:2] == ca[:2]                                   # the decisions do not depend on the samples
+    assert a.p["xyz"].shape == c.p["xyz"].shape and not torch.equal(a.p["xyz"], c.p["xyz"])
+    assert not torch.equal(a.replica_checksum(), c.replica_checksum())

@@ -204,3 +204,44 @@ def test_tile_id_bits_is_the_bit_length_of_the_largest_id(tmp_path):
     assert got == {1: 1, 2: 1, 3: 2, 4096: 12, 4097: 13, 8160: 13, 16384: 14}
     for n, b in got.items():
         assert (n - 1) < (1 << b) and (n <= 2 or (n - 1) >= (1 << (b - 1)))
+
+
+def _stats_rank_main(rank, world, port, N, out_dir):
+    from soar_b200.densify import STATS, allreduce_densify_stats
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(100 + rank)          # every rank saw different views
+    stats = {k: torch.rand(N, generator=g) for k in STATS}
+    stats["max_radii2D"] = torch.randint(0, 50, (N,), generator=g).float()
+    allreduce_densify_stats(stats)
+    torch.save(stats, os.path.join(out_dir, f"stats{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_densify_statistics_are_identical_on_every_rank_after_the_allreduce_gloo(tmp_path):
+    """clone / split / prune decisions must come from statistics that are the same on
+    every replica — sums of the per-rank accumulators, maximum of max_radii2D. world_size 2, gloo."""
+    from soar_b200.densify import STATS
+    world, N = 2, 1001
+    mp.spawn(_stats_rank_main, args=(world, _free_port(), N, str(tmp_path)), nprocs=world, join=True)
+    got = [torch.load(os.path.join(tmp_path, f"stats{r}.pt")) for r in range(world)]
+    local = []
+    for r in range(world):
+        g = torch.Generator().manual_seed(100 + r)
+        st = {k: torch.rand(N, generator=g) for k in STATS}
+        st["max_radii2D"] = torch.randint(0, 50, (N,), generator=g).float()
+        local.append(st)
+    for k in STATS:
+        assert torch.equal(got[0][k], got[1][k]), k           # bit-identical across ranks
+        want = (torch.maximum(local[0][k], local[1][k]) if k == "max_radii2D" else local[0][k] + local[1][k])
+        assert torch.equal(got[0][k], want), k
+
+
+def test_replica_generator_is_a_function_of_seed_and_cycle_only():
+    from soar_b200.densify import replica_generator
+    std = torch.full((64, 3), 0.1)
+    draw = lambda seed, cycle: torch.normal(mean=torch.zeros_like(std), std=std,
+                                            generator=replica_generator("cpu", seed, cycle))
+    assert torch.equal(draw(7, 1), draw(7, 1))
+    assert not torch.equal(draw(7, 1), draw(7, 2))
+    assert not torch.equal(draw(7, 1), draw(8, 1))
