@@ -1168,6 +1168,12 @@ class AvatarWorkload:
                            colors=g["colors"].requires_grad_(True),
                            scale2d=torch.full((N, 1), 0.004, device=device).requires_grad_(True))
         self.flat = FlatGrads(self.params)
+        # Adam over the four parameter groups (the reference: torch.optim.Adam(l, lr=0.0, eps=1e-15) with
+        # per-group rates, TS/geometry/surfel_base.py:596-681), one fused launch per step reading the
+        # all-reduced flat buffer. Rates are small so the scene stays the benchmarked one over the run.
+        self.moments = {k: (torch.zeros_like(v), torch.zeros_like(v)) for k, v in self.params.items()}
+        self.adam_lr = dict(points=1.6e-7, rot=1e-6, colors=2.5e-6, scale2d=5e-7)
+        self.adam_steps = 0
         self.bg = torch.zeros(3, device=device)
         gen = torch.Generator(device).manual_seed(rank)
         self.cot = {k: torch.randn(ch, H, W, device=device, generator=gen) for k, ch in
@@ -1177,6 +1183,22 @@ class AvatarWorkload:
         quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
         if quiet is not None:   # the leaves are accumulated on the caller's stream on purpose
             quiet(False)
+
+    def adam_step(self):
+        """optimizer.step() of the four groups: soar_adam_step, gradients = the slices of the flat buffer."""
+        import ctypes
+        from soar_b200 import _capi
+        lib = _capi.load()
+        self.adam_steps += 1
+        table = (_capi.SoarAdamGroup * _capi.ADAM_MAX_GROUPS)()
+        for i, (k, p_) in enumerate(self.params.items()):
+            e = table[i]
+            m, v = self.moments[k]
+            e.param, e.grad = p_.data_ptr(), self.flat.grad(k).data_ptr()
+            e.exp_avg, e.exp_avg_sq = m.data_ptr(), v.data_ptr()
+            e.numel, e.lr, e.step = p_.numel(), self.adam_lr[k], self.adam_steps
+        _capi.check(lib.soar_adam_step(table, len(self.params), 0.9, 0.999, 1e-15,
+                                       ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)), "soar_adam_step")
 
     def step(self, allreduce=True, overlapped=True):
         if overlapped:
@@ -1195,6 +1217,7 @@ class AvatarWorkload:
             self.visible = out["visibility_filter"]
         if allreduce:
             self.flat.allreduce()
+        self.adam_step()
 
     def step_overlapped(self, allreduce=True):
         """The same step with its independent pieces on separate CUDA streams: distCUDA2 of the
@@ -1237,6 +1260,7 @@ class AvatarWorkload:
             main.wait_stream(s)
         if allreduce:
             self.flat.allreduce()
+        self.adam_step()
 
 
 def run_c5(args, world, rank, local, device):
@@ -1307,7 +1331,10 @@ def run_c5(args, world, rank, local, device):
                 "allreduce": verified, "allreduce_ms": ar_ms,
                 "allreduce_share_of_step": (ar_ms / (ms / args.steps)) if ar_ms else None,
                 "step_layout": ("distCUDA2 and the three views on separate CUDA streams, one backward of the "
-                                "summed loss" if overlapped else "one stream, one backward per view"),
+                                "summed loss" if overlapped else "one stream, one backward per view")
+                               + "; then the gradient all-reduce and one fused Adam launch over the four groups",
+                "adam_share_of_step": (kern.get("adam_step", 0.0) / (ms / args.steps)),
+                "not_in_step": "the prune/clone/split cycle (P would change mid-run); measured alone under `densify`",
                 "kernel_ms_per_step": kern, "kernel_ms_sum": round(sum(kern.values()), 3),
                 "kernel_ms_note": "per-kernel times of one extra step run on ONE stream"}
         print(json.dumps(line), flush=True)
